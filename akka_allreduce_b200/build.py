@@ -1,0 +1,141 @@
+"""In-tree builder for the native libraries.
+
+Two artefacts land in ``akka_allreduce_b200/_native/`` (git-ignored, shipped to the GPU box
+by the snapshot):
+
+* ``_aar_host*.so``   - C++17 host library (protocol engines, buffers, bus, TCP nodes),
+                        pybind11, built with g++.
+* ``libaar_cuda.so``  - sm_100a CUDA kernels + symmetric heap behind a C ABI
+                        (``include/aar_b200.h``), built with nvcc, loaded through ctypes.
+
+``python -m akka_allreduce_b200.build`` builds both; ``--host`` / ``--cuda`` pick one.
+Rebuilds only when a source or header is newer than the artefact.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+import sysconfig
+from pathlib import Path
+
+PKG = Path(__file__).resolve().parent
+ROOT = PKG.parent
+NATIVE = PKG / "_native"
+CSRC = ROOT / "csrc"
+INCLUDE = ROOT / "include"
+
+HOST_SOURCES = [
+    "host/buffers.cc",
+    "host/worker_engine.cc",
+    "host/master_engine.cc",
+    "host/local_bus.cc",
+    "host/node.cc",
+    "host/node_bindings.cc",
+    "host/bindings.cc",
+]
+CUDA_SOURCES = [
+    "cuda/fused_allreduce.cu",
+    "cuda/sym_heap.cu",
+]
+CUDA_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+
+
+def _newer_than(target: Path, deps: list[Path]) -> bool:
+    if not target.exists():
+        return True
+    t = target.stat().st_mtime
+    return any(d.stat().st_mtime > t for d in deps if d.exists())
+
+
+def _headers() -> list[Path]:
+    return list(INCLUDE.rglob("*.h")) + list(CSRC.rglob("*.h")) + list(CSRC.rglob("*.cuh"))
+
+
+def _run(cmd: list[str]) -> None:
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    if proc.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+        raise RuntimeError(f"native build failed: {cmd[0]} exited {proc.returncode}")
+    if proc.stderr.strip() and os.environ.get("AAR_BUILD_VERBOSE"):
+        sys.stderr.write(proc.stderr)
+
+
+def host_library_path() -> Path:
+    return NATIVE / ("_aar_host" + sysconfig.get_config_var("EXT_SUFFIX"))
+
+
+def cuda_library_path() -> Path:
+    return NATIVE / "libaar_cuda.so"
+
+
+def build_host(force: bool = False) -> Path:
+    import pybind11
+
+    NATIVE.mkdir(exist_ok=True)
+    out = host_library_path()
+    srcs = [CSRC / s for s in HOST_SOURCES]
+    if not force and not _newer_than(out, srcs + _headers()):
+        return out
+    objdir = ROOT / "build" / "host"
+    objdir.mkdir(parents=True, exist_ok=True)
+    common = [
+        "g++", "-std=c++17", "-O2", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-parameter",
+        f"-I{INCLUDE}", f"-I{CSRC / 'host'}", f"-I{pybind11.get_include()}",
+        f"-I{sysconfig.get_paths()['include']}",
+    ]
+    objs = []
+    procs = []
+    for s in srcs:
+        o = objdir / (s.stem + ".o")
+        objs.append(o)
+        if force or _newer_than(o, [s] + _headers()):
+            procs.append((s, subprocess.Popen(common + ["-c", str(s), "-o", str(o)],
+                                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for s, p in procs:
+        log, _ = p.communicate()
+        if p.returncode != 0:
+            sys.stderr.write(log)
+            raise RuntimeError(f"native build failed compiling {s}")
+    _run(["g++", "-shared", "-o", str(out)] + [str(o) for o in objs] + ["-lpthread"])
+    return out
+
+
+def nvcc_path() -> str | None:
+    cand = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    return cand if Path(cand).exists() else None
+
+
+def build_cuda(force: bool = False) -> Path:
+    NATIVE.mkdir(exist_ok=True)
+    out = cuda_library_path()
+    srcs = [CSRC / s for s in CUDA_SOURCES if (CSRC / s).exists()]
+    if not force and not _newer_than(out, srcs + _headers()):
+        return out
+    nvcc = nvcc_path()
+    if nvcc is None:
+        raise RuntimeError("nvcc not found; cannot build the sm_100a kernels")
+    cmd = [nvcc, "-std=c++17", "-O3", "-lineinfo", *CUDA_ARCH, "-Xcompiler", "-fPIC", "-shared",
+           "-Xptxas", "-v", f"-I{INCLUDE}", f"-I{CSRC / 'cuda'}", "-o", str(out)] + [str(s) for s in srcs] + ["-lcuda"]
+    proc = subprocess.run(cmd, capture_output=True, text=True)
+    (ROOT / "build").mkdir(exist_ok=True)
+    (ROOT / "build" / "ptxas_v.log").write_text(proc.stdout + proc.stderr)
+    if proc.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+        raise RuntimeError("nvcc failed")
+    return out
+
+
+def build_all(force: bool = False) -> None:
+    build_host(force)
+    build_cuda(force)
+
+
+if __name__ == "__main__":
+    args = set(sys.argv[1:])
+    force = "--force" in args
+    if "--host" in args or not (args - {"--force"}):
+        print(build_host(force))
+    if "--cuda" in args or not (args - {"--force"}):
+        print(build_cuda(force))

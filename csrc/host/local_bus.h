@@ -1,0 +1,43 @@
+// Deterministic in-process message bus.
+//
+// Plays the part Akka's mailboxes play in the reference's single-actor tests
+// (src/test/scala/AllreduceSpec.scala:812-818): every endpoint is either a real engine
+// or a probe that records what it receives.  One global FIFO keeps delivery order
+// reproducible; a message an engine sends to itself goes to the back of the queue, the
+// way `self ! msg` does.
+#pragma once
+#include <deque>
+#include <functional>
+#include <map>
+#include <utility>
+#include <vector>
+
+#include "messages.h"
+
+namespace aar {
+
+class LocalBus : public Mailer {
+ public:
+  using Handler = std::function<void(const Message&)>;
+
+  Endpoint add_endpoint(Handler h);  // engine
+  Endpoint add_probe();              // records
+  void rebind(Endpoint ep, Handler h) { handlers_[ep] = std::move(h); }
+
+  void send(Endpoint to, Message msg) override;
+  // Delivers until the queue drains (or `max_steps` deliveries); returns deliveries made.
+  size_t run(size_t max_steps = 1u << 22);
+  size_t pending() const { return queue_.size(); }
+
+  std::vector<Message>& inbox(Endpoint probe) { return inboxes_[probe]; }
+  size_t dropped() const { return dropped_; }
+
+ private:
+  Endpoint next_ = 1;
+  std::map<Endpoint, Handler> handlers_;
+  std::map<Endpoint, std::vector<Message>> inboxes_;
+  std::deque<std::pair<Endpoint, Message>> queue_;
+  size_t dropped_ = 0;
+};
+
+}  // namespace aar

@@ -1,0 +1,72 @@
+#include "master_engine.h"
+
+#include <cstdio>
+
+#include "aar/protocol_math.h"
+
+namespace aar {
+
+MasterEngine::MasterEngine(Endpoint self, MasterConfig cfg, Mailer* mailer, bool verbose)
+    : self_(self), cfg_(cfg), mailer_(mailer), verbose_(verbose) {}
+
+int MasterEngine::member_up(Endpoint worker) {
+  // Ids follow arrival order.  The reference uses workers.size, which collides with a
+  // live id after a removal; a monotonic counter is identical until the first removal
+  // and never reuses an id afterwards.
+  const int id = next_id_++;
+  workers_[id] = worker;
+  if (static_cast<int>(workers_.size()) >= cfg_.total_workers && round_ == -1) {
+    if (verbose_)
+      std::printf("----%zu (out of %d) workers are up\n", workers_.size(), cfg_.total_workers);
+    init_workers();
+    round_ = 0;
+    start_allreduce();
+  }
+  return id;
+}
+
+void MasterEngine::terminated(Endpoint worker) {
+  for (auto it = workers_.begin(); it != workers_.end();)
+    it = (it->second == worker) ? workers_.erase(it) : std::next(it);
+}
+
+void MasterEngine::handle(const Message& m) {
+  const auto* c = std::get_if<CompleteAllreduce>(&m);
+  if (!c || c->round != round_) return;  // only the current round counts
+  num_complete_ += 1;
+  if (master_gate(num_complete_, cfg_.total_workers, cfg_.th_allreduce)) {
+    if (round_ < cfg_.max_round) {
+      if (verbose_)
+        std::printf("----%d (out of %d) workers complete round %d\n", num_complete_,
+                    cfg_.total_workers, round_);
+      round_ += 1;
+      start_allreduce();
+    } else {
+      done_last_ = true;  // rounds 0..max_round inclusive have been run
+    }
+  }
+}
+
+void MasterEngine::init_workers() {
+  for (const auto& [id, ep] : workers_) {
+    InitWorkers init;
+    init.workers = workers_;
+    init.worker_num = cfg_.total_workers;
+    init.master = self_;
+    init.dest_id = id;
+    init.th_reduce = cfg_.th_reduce;
+    init.th_complete = cfg_.th_complete;
+    init.max_lag = cfg_.max_lag;
+    init.data_size = cfg_.data_size;
+    init.max_chunk_size = cfg_.max_chunk_size;
+    mailer_->send(ep, std::move(init));
+  }
+}
+
+void MasterEngine::start_allreduce() {
+  if (verbose_) std::printf("\n----Start allreduce round %d\n", round_);
+  num_complete_ = 0;
+  for (const auto& [id, ep] : workers_) mailer_->send(ep, StartAllreduce{round_});
+}
+
+}  // namespace aar
