@@ -1,0 +1,117 @@
+"""AllreduceMaster: the rank-0 coordinator and its launcher.
+
+Counterpart of the reference's master actor + ``object AllreduceMaster`` launcher
+(AllreduceMaster.scala:12-146): listens on the configured port, waits for ``totalSize`` workers,
+assigns ids in arrival order, broadcasts InitWorkers once, and gates every round on
+``thAllreduce``.  The gate itself runs in the C++ ``MasterNode``.
+
+CLI (positional order of the reference, README.md:3)::
+
+    python -m akka_allreduce_b200.master [PORT=2551] [numOfWorkers=2] [dataSize=5*numOfWorkers] [maxChunkSize=2]
+        [--config FILE] [--thAllreduce F] [--thReduce F] [--thComplete F] [--maxLag N] [--maxRound N]
+"""
+from __future__ import annotations
+
+import argparse
+import sys
+
+from . import host
+from .config import AllreduceConfig, DataConfig, ThresholdConfig, WorkerConfig, load_config
+from .utils.logging import get_logger
+
+
+class AllreduceMaster:
+    def __init__(self, config: AllreduceConfig, verbose: bool = False):
+        self.config = config
+        self.log = get_logger("master", config.cluster.loglevel)
+        opts = host.MasterNodeOptions()
+        opts.down_after_s = config.cluster.downAfter
+        opts.verbose = verbose
+        self._node = host.MasterNode(config.master_config(), opts)
+        self.port = None
+
+    def start(self) -> int:
+        c = self.config
+        self.port = self._node.listen(c.cluster.host, c.cluster.port)
+        self.log.info("-------\n Port = %s \n Number of Workers = %s \n Message Size = %s \n Max Chunk Size = %s",
+                      self.port, c.worker.totalSize, c.data.dataSize, c.data.maxChunkSize)
+        self._node.start()
+        return self.port
+
+    def wait(self, timeout: float = 3600.0) -> bool:
+        """Blocks until round ``maxRound`` has passed the gate (or the timeout expires)."""
+        return self._node.wait_finished(timeout)
+
+    def stop(self) -> None:
+        self._node.stop()
+
+    round = property(lambda self: self._node.round)
+    registered = property(lambda self: self._node.registered)
+    alive = property(lambda self: self._node.alive)
+
+    # -- reference-style entry points (AllreduceMaster.scala:138-144) ----------------------------
+    @staticmethod
+    def start_up(port: int | str | None = None, thresholds: ThresholdConfig | None = None,
+                 data_config: DataConfig | None = None, worker_config: WorkerConfig | None = None,
+                 config: AllreduceConfig | None = None, verbose: bool = True) -> "AllreduceMaster":
+        cfg = config or AllreduceConfig()
+        if thresholds:
+            cfg.thresholds = thresholds
+        if data_config:
+            cfg.data = data_config
+        if worker_config:
+            cfg.worker = worker_config
+        if port is not None:
+            cfg.cluster.port = int(port)
+        m = AllreduceMaster(cfg, verbose=verbose)
+        m.start()
+        return m
+
+
+def build_config(argv: list[str]) -> AllreduceConfig:
+    ap = argparse.ArgumentParser(prog="akka_allreduce_b200.master", description=__doc__,
+                                 formatter_class=argparse.RawDescriptionHelpFormatter)
+    ap.add_argument("port", nargs="?", type=int)
+    ap.add_argument("numOfWorkers", nargs="?", type=int)
+    ap.add_argument("dataSize", nargs="?", type=int)
+    ap.add_argument("maxChunkSize", nargs="?", type=int)
+    ap.add_argument("--config")
+    for k in ("thAllreduce", "thReduce", "thComplete"):
+        ap.add_argument("--" + k, type=float)
+    for k in ("maxLag", "maxRound"):
+        ap.add_argument("--" + k, type=int)
+    ap.add_argument("--host")
+    a = ap.parse_args(argv)
+    cfg = load_config(a.config)
+    if a.numOfWorkers is not None:
+        cfg.worker.totalSize = a.numOfWorkers
+        if a.dataSize is None and a.config is None:
+            cfg.data.dataSize = 5 * a.numOfWorkers  # AllreduceMaster.scala:103
+    overrides = {"port": a.port, "dataSize": a.dataSize, "maxChunkSize": a.maxChunkSize, "host": a.host,
+                 "thAllreduce": a.thAllreduce, "thReduce": a.thReduce, "thComplete": a.thComplete,
+                 "maxLag": a.maxLag, "maxRound": a.maxRound}
+    return _with(cfg, overrides)
+
+
+def _with(cfg: AllreduceConfig, overrides: dict) -> AllreduceConfig:
+    from .config import _apply
+
+    _apply(cfg, {k: v for k, v in overrides.items() if v is not None})
+    return cfg
+
+
+def main(argv: list[str] | None = None) -> int:
+    cfg = build_config(sys.argv[1:] if argv is None else argv)
+    master = AllreduceMaster(cfg, verbose=True)
+    master.start()
+    try:
+        master.wait()
+    except KeyboardInterrupt:
+        pass
+    finally:
+        master.stop()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

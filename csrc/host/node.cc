@@ -184,7 +184,7 @@ TcpNode::Conn* TcpNode::conn(int id) {
   return it == conns_.end() ? nullptr : &it->second;
 }
 
-int TcpNode::connect_to(const PeerAddress& a) {
+int TcpNode::connect_to(const PeerAddress& a, int retries) {
   const int fd = socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
   if (fd < 0) throw std::runtime_error("socket() failed");
   sockaddr_in sa{};
@@ -192,9 +192,9 @@ int TcpNode::connect_to(const PeerAddress& a) {
   sa.sin_port = htons(static_cast<uint16_t>(a.port));
   inet_pton(AF_INET, a.host.c_str(), &sa.sin_addr);
   int rc = -1;
-  for (int attempt = 0; attempt < 200; ++attempt) {  // the peer may still be binding: retry ~10 s
+  for (int attempt = 0; attempt <= retries; ++attempt) {  // 50 ms apart
     rc = ::connect(fd, reinterpret_cast<sockaddr*>(&sa), sizeof(sa));
-    if (rc == 0 || (errno != ECONNREFUSED && errno != EINTR)) break;
+    if (rc == 0 || (errno != ECONNREFUSED && errno != EINTR) || attempt == retries) break;
     std::this_thread::sleep_for(std::chrono::milliseconds(50));
   }
   if (rc != 0) {
@@ -520,7 +520,7 @@ WorkerNode::WorkerNode(PeerAddress master, DataSource source, DataSink sink, Wor
 
 void WorkerNode::begin() {
   if (listen_port_ == 0) listen_on("127.0.0.1", 0);
-  master_conn_ = connect_to(master_addr_);
+  master_conn_ = connect_to(master_addr_, 400);  // the master may still be starting: retry ~20 s
   Writer w;
   w.put<int32_t>(listen_port_);
   w.str(listen_host_);
@@ -532,7 +532,15 @@ void WorkerNode::begin() {
 int WorkerNode::conn_for_peer(int peer_id) {
   auto it = peer_conn_.find(peer_id);
   if (it != peer_conn_.end() && conn(it->second)) return it->second;
-  const int id = connect_to(peer_addr_.at(peer_id));
+  if (dead_peers_.count(peer_id)) throw std::runtime_error("peer is down");
+  int id;
+  try {
+    // Peers listen before they register, so a refused connection means the peer is gone.
+    id = connect_to(peer_addr_.at(peer_id), 0);
+  } catch (const std::exception&) {
+    dead_peers_.insert(peer_id);
+    throw;
+  }
   peer_conn_[peer_id] = id;
   Writer w;
   w.put<int32_t>(worker_id_.load());
@@ -634,8 +642,14 @@ void WorkerNode::on_closed(int conn_id) {
     shutdown_ = true;
     state_cv_.notify_all();
   }
-  for (auto it = peer_conn_.begin(); it != peer_conn_.end();)
-    it = (it->second == conn_id) ? peer_conn_.erase(it) : std::next(it);
+  for (auto it = peer_conn_.begin(); it != peer_conn_.end();) {
+    if (it->second == conn_id) {
+      dead_peers_.insert(it->first);  // messages to it become dead letters from now on
+      it = peer_conn_.erase(it);
+    } else {
+      ++it;
+    }
+  }
 }
 
 void WorkerNode::on_tick() {

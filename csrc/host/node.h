@@ -21,6 +21,7 @@
 #include <map>
 #include <memory>
 #include <mutex>
+#include <set>
 #include <string>
 #include <thread>
 #include <vector>
@@ -77,7 +78,7 @@ class TcpNode : public Mailer {
   virtual void on_tick() {}
   virtual void on_local(const Message& m) {}  // message an engine sent to itself
 
-  int connect_to(const PeerAddress& a);  // returns conn id (blocking connect, IO thread)
+  int connect_to(const PeerAddress& a, int retries = 0);  // returns conn id (blocking connect)
   void queue_frame(int conn_id, Frame kind, const std::vector<uint8_t>& payload);  // any thread
   void queue_local(Message m);                                                     // any thread
   void close_conn(int conn_id);
@@ -180,6 +181,7 @@ class WorkerNode : public TcpNode {
   int master_conn_ = -1;
   std::map<int, PeerAddress> peer_addr_;
   std::map<int, int> peer_conn_;
+  std::set<int> dead_peers_;
   std::atomic<int> worker_id_{-1};
   std::atomic<int> rounds_done_{0};
   std::chrono::steady_clock::time_point last_beat_;

@@ -1,0 +1,148 @@
+"""Config file, CLI argument handling, and the TCP coordinator + CPU workers (multi-process plumbing)."""
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from akka_allreduce_b200 import AllReduceInput, AllreduceConfig, load_config
+from akka_allreduce_b200.config import parse_hocon, DEFAULT_CONFIG_PATH
+from akka_allreduce_b200.master import AllreduceMaster, build_config
+from akka_allreduce_b200.worker import AllreduceWorker
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_hocon_subset():
+    t = parse_hocon('a { b = 1, c: "x y" }\n a.d = 2.5 # c\n e = [1, 2]\n f { g { h = 10s } }\n// c2\n i = off')
+    assert t == {"a": {"b": 1, "c": "x y", "d": 2.5}, "e": [1, 2], "f": {"g": {"h": 10.0}}, "i": False}
+
+
+def test_default_config_file_matches_reference_hardcoded_values():
+    """AllreduceMaster.scala:98-107: maxLag 1, maxRound 100, th 1/1/0.8, 2 workers, dataSize 10, chunk 2."""
+    c = load_config(DEFAULT_CONFIG_PATH)
+    assert (c.thresholds.thAllreduce, c.thresholds.thReduce, c.thresholds.thComplete) == (1.0, 1.0, 0.8)
+    assert (c.worker.totalSize, c.worker.maxLag, c.data.dataSize, c.data.maxChunkSize, c.data.maxRound) == (2, 1, 10, 2, 100)
+    assert c.cluster.port == 2551 and c.cluster.downAfter == 10.0
+
+
+def test_reference_akka_conf_is_accepted(tmp_path):
+    """The reference's own application.conf parses; port/loglevel/auto-down are picked up."""
+    ref = "/root/reference/src/main/resources/application.conf"
+    if not os.path.exists(ref):
+        pytest.skip("reference tree not mounted")
+    text = open(ref).read().replace("${user.dir}/target/native", '"target/native"')
+    p = tmp_path / "application.conf"
+    p.write_text("\n".join(l for l in text.splitlines() if not l.startswith("akka.")))
+    c = load_config(p)
+    assert c.cluster.downAfter == 10.0 and c.cluster.loglevel == "INFO" and c.cluster.host == "127.0.0.1"
+
+
+def test_master_cli_positional_order():
+    """README.md:3 — PORT numOfWorkers dataSize maxChunkSize; dataSize defaults to 5*numOfWorkers."""
+    c = build_config(["2600", "4", "778", "3", "--maxLag", "3", "--thComplete", "1.0"])
+    assert (c.cluster.port, c.worker.totalSize, c.data.dataSize, c.data.maxChunkSize) == (2600, 4, 778, 3)
+    assert c.worker.maxLag == 3 and c.thresholds.thComplete == 1.0
+    assert build_config(["2600", "6"]).data.dataSize == 30
+    assert build_config([]).cluster.port == 2551
+
+
+def _cluster(P, n, mc, rounds, th=(1.0, 1.0, 1.0), max_lag=1):
+    cfg = AllreduceConfig()
+    cfg.cluster.port = 0
+    cfg.worker.totalSize, cfg.worker.maxLag = P, max_lag
+    cfg.data.dataSize, cfg.data.maxChunkSize, cfg.data.maxRound = n, mc, rounds
+    cfg.thresholds.thAllreduce, cfg.thresholds.thReduce, cfg.thresholds.thComplete = th
+    return cfg
+
+
+def test_tcp_cluster_python_callbacks():
+    """3 workers with Python source/sink over real sockets; thresholds 1 -> exact sums."""
+    P, n = 3, 20
+    cfg = _cluster(P, n, 3, 12, max_lag=2)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    outs = [dict() for _ in range(P)]
+    workers = []
+    for i in range(P):
+        def source(req):
+            return AllReduceInput(np.arange(n, dtype=np.float32) + req.iteration)
+
+        def sink(out, i=i):
+            outs[i][out.iteration] = (np.array(out.data), np.array(out.count))
+
+        w = AllreduceWorker(source, sink, master_port=port)
+        w.start()
+        workers.append(w)
+    try:
+        assert master.wait(30.0), f"master stuck at round {master.round}"
+        assert all(w.wait(10.0) for w in workers)
+    finally:
+        for w in workers:
+            w.stop()
+        master.stop()
+    assert sorted(w.id for w in workers) == [0, 1, 2]
+    for o in outs:
+        assert sorted(o) == list(range(13))
+        for it, (d, c) in o.items():
+            assert (d == P * (np.arange(n, dtype=np.float32) + it)).all() and (c == P).all()
+
+
+def test_tcp_cluster_survives_dead_worker_with_thresholds():
+    """Failure path (AllreduceMaster.scala:46-52): one of 4 workers dies; thresholds 0.75 keep rounds going
+    and the master drops it from the set."""
+    P, n = 4, 16
+    cfg = _cluster(P, n, 2, 60, th=(0.75, 0.75, 0.75), max_lag=3)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    done = [0] * P
+    workers = []
+    for i in range(P):
+        def source(req):
+            return AllReduceInput(np.ones(n, dtype=np.float32))
+
+        def sink(out, i=i):
+            done[i] = max(done[i], out.iteration)
+            got = np.array(out.count) > 0
+            assert (np.array(out.data)[got] == np.array(out.count)[got]).all()  # sum of ones == count
+
+        w = AllreduceWorker(source, sink, master_port=port)
+        w.start()
+        workers.append(w)
+    try:
+        t0 = time.time()
+        while master.round < 5 and time.time() - t0 < 20:
+            time.sleep(0.01)
+        workers[3].stop()  # kill one
+        assert master.wait(30.0), f"master stuck at round {master.round}"
+        assert master.alive == 3
+    finally:
+        for w in workers[:3]:
+            w.stop()
+        master.stop()
+    assert all(d >= 55 for d in done[:3])
+
+
+def test_cli_processes_default_plumbing_config():
+    """BASELINE config 1: master + 2 worker processes via the CLIs, dataSize 10, chunk 2 (CPU only)."""
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    port = 27000 + os.getpid() % 2000
+    m = subprocess.Popen([sys.executable, "-m", "akka_allreduce_b200.master", str(port), "2", "10", "2",
+                          "--maxRound", "200", "--thComplete", "1.0"], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    ws = [subprocess.Popen([sys.executable, "-m", "akka_allreduce_b200.worker", "0", "10", "--master-port", str(port),
+                            "--checkpoint", "50", "--assert-multiple", "2"], env=env, stdout=subprocess.PIPE,
+                           stderr=subprocess.STDOUT, text=True) for _ in range(2)]
+    try:
+        outs = [w.communicate(timeout=60)[0] for w in ws]
+        mout = m.communicate(timeout=30)[0]
+    finally:
+        for p in ws + [m]:
+            if p.poll() is None:
+                p.kill()
+    assert m.returncode == 0, mout
+    for w, o in zip(ws, outs):
+        assert w.returncode == 0, o
+        assert "MBytes/sec" in o and "----Data output at #50" in o
