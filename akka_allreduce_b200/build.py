@@ -117,7 +117,7 @@ def build_cuda(force: bool = False) -> Path:
     if nvcc is None:
         raise RuntimeError("nvcc not found; cannot build the sm_100a kernels")
     cmd = [nvcc, "-std=c++17", "-O3", "-lineinfo", *CUDA_ARCH, "-Xcompiler", "-fPIC", "-shared",
-           "-Xptxas", "-v", f"-I{INCLUDE}", f"-I{CSRC / 'cuda'}", "-o", str(out)] + [str(s) for s in srcs] + ["-lcuda"]
+           "-Xptxas", "-v", f"-I{INCLUDE}", f"-I{CSRC / 'cuda'}", "-o", str(out)] + [str(s) for s in srcs]
     proc = subprocess.run(cmd, capture_output=True, text=True)
     (ROOT / "build").mkdir(exist_ok=True)
     (ROOT / "build" / "ptxas_v.log").write_text(proc.stdout + proc.stderr)

@@ -1,0 +1,102 @@
+"""ctypes binding of ``libaar_cuda.so`` (C ABI in ``include/aar_b200.h``).
+
+The CUDA path fails loudly: if the library cannot be built or loaded on a machine that has a
+GPU, importing this module raises instead of falling back to eager PyTorch.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+from .. import build as _build
+
+MAX_RANKS = 16
+F32, BF16 = 0, 1
+ALGO_TWOSHOT, ALGO_ONESHOT, ALGO_NVLS = 0, 1, 2
+ALGO_NAMES = {"twoshot": ALGO_TWOSHOT, "oneshot": ALGO_ONESHOT, "nvls": ALGO_NVLS}
+
+
+class AarLaunch(C.Structure):
+    """Mirror of ``struct AarLaunch`` — keep field order and types in sync with the header."""
+
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32), ("emu", C.c_int32),
+        ("algo", C.c_int32), ("in_dtype", C.c_int32), ("wire_dtype", C.c_int32),
+        ("ctas", C.c_int32), ("use_tma", C.c_int32),
+        ("n", C.c_int64), ("max_chunk", C.c_int64), ("os_cap", C.c_int64), ("block_step", C.c_int64),
+        ("L", C.c_int32), ("slot", C.c_int32),
+        ("tag", C.c_uint32),
+        ("req_reduce", C.c_int32), ("req_complete", C.c_int32), ("gate_count", C.c_int32),
+        ("normalize", C.c_int32),
+        ("scale", C.c_float),
+        ("skip_dest_mask", C.c_uint32 * MAX_RANKS),
+        ("mute_mask", C.c_uint32),
+        ("delay_ns", C.c_uint64 * MAX_RANKS),
+        ("timeout_ns", C.c_uint64),
+        ("src", C.c_void_p * MAX_RANKS),
+        ("out", C.c_void_p * MAX_RANKS),
+        ("counts", C.c_void_p * MAX_RANKS),
+        ("sym", C.c_void_p * MAX_RANKS),
+        ("mc_base", C.c_void_p),
+        ("scratch", C.c_void_p * MAX_RANKS),
+        ("host_flags", C.c_void_p),
+    ]
+
+
+_lib = None
+
+
+def library_path() -> Path:
+    return _build.cuda_library_path()
+
+
+def lib() -> C.CDLL:
+    """Loads (building first if needed) the CUDA library and declares its prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.build_cuda()
+    l = C.CDLL(str(path))
+    i64, i32, vp = C.c_int64, C.c_int, C.c_void_p
+    l.aar_sym_bytes.restype = i64
+    l.aar_sym_bytes.argtypes = [i64, i64, i32, i32, i32, i64, i64]
+    l.aar_sym_flag_bytes.restype = i64
+    l.aar_sym_flag_bytes.argtypes = [i64, i64, i32, i32, i32, i64, i64]
+    l.aar_scratch_bytes.restype = i64
+    l.aar_scratch_bytes.argtypes = [i64, i64, i32, i64]
+    l.aar_allreduce_round.restype = i32
+    l.aar_allreduce_round.argtypes = [C.POINTER(AarLaunch), vp]
+    l.aar_max_emu_ctas.restype = i32
+    l.aar_max_emu_ctas.argtypes = [i32, i32]
+    l.aar_heap_create.restype = i32
+    l.aar_heap_create.argtypes = [C.POINTER(vp), i32, i32, i32, i64, C.c_char_p, i32]
+    l.aar_heap_ptrs.restype = i32
+    l.aar_heap_ptrs.argtypes = [vp, C.POINTER(vp), C.POINTER(vp)]
+    l.aar_heap_bytes.restype = i64
+    l.aar_heap_bytes.argtypes = [vp]
+    l.aar_heap_destroy.restype = i32
+    l.aar_heap_destroy.argtypes = [vp]
+    l.aar_last_error.restype = C.c_char_p
+    l.aar_last_error.argtypes = []
+    _lib = l
+    return l
+
+
+class AarError(RuntimeError):
+    pass
+
+
+def check(rc: int, what: str = "") -> int:
+    if rc < 0:
+        raise AarError(f"{what or 'libaar_cuda'} failed ({rc}): {lib().aar_last_error().decode()}")
+    return rc
+
+
+def dtype_code(torch_dtype) -> int:
+    import torch
+
+    if torch_dtype == torch.float32:
+        return F32
+    if torch_dtype == torch.bfloat16:
+        return BF16
+    raise AarError(f"unsupported dtype {torch_dtype}; float32 and bfloat16 are")

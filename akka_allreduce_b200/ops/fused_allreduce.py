@@ -1,0 +1,140 @@
+"""Launchers for the fused scatter -> reduce -> broadcast kernel.
+
+``RoundLauncher`` owns everything a rank needs to run rounds on its GPU — scratch, mapped host
+flags, the geometry — and fills the ``AarLaunch`` struct.  Two front ends use it:
+
+* ``EmulatedCluster`` — all ``world`` ranks on ONE GPU in one cooperative launch (rank =
+  ``blockIdx.y``).  Ranks that wait on each other must never be separate launches on one device,
+  so this is how the full multi-rank protocol (thresholds, stragglers, lag ring) is exercised
+  on a single B200, in tests and in the 1-GPU benchmark.
+* ``akka_allreduce_b200.parallel.engine.DeviceAllreduce`` — one rank per process/GPU over the
+  symmetric heap (NVLink peer pointers).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import torch
+
+from . import cuda as K
+from .geometry import Geometry, default_ctas, gate_count
+
+
+@dataclass
+class Injection:
+    """Straggler injection for one round (tests and the straggler benchmark)."""
+
+    mute: int = 0                                   # bit r: rank r scatters nothing this round
+    skip: dict = field(default_factory=dict)        # rank -> bitmask of destinations it skips
+    delay_ns: dict = field(default_factory=dict)    # rank -> idle time before it starts
+
+
+class RoundLauncher:
+    def __init__(self, geo: Geometry, dtype: torch.dtype, wire_dtype: torch.dtype, th_reduce: float,
+                 th_complete: float, th_allreduce: float | None, ctas: int, timeout_ms: float,
+                 scale: float = 1.0, normalize: bool = False, os_cap: int = 0, algo: int = K.ALGO_TWOSHOT):
+        self.lib = K.lib()
+        self.geo = geo
+        self.dtype, self.wire_dtype = dtype, wire_dtype
+        self.in_code, self.wire_code = K.dtype_code(dtype), K.dtype_code(wire_dtype)
+        self.os_cap = os_cap
+        self.algo = algo
+        self.ctas = ctas
+        self.timeout_ns = int(timeout_ms * 1e6)
+        self.scale, self.normalize = scale, normalize
+        self.req_reduce = geo.req_reduce(th_reduce)
+        self.req_complete = geo.req_complete(th_complete)
+        self.gate = 0 if th_allreduce is None else gate_count(th_allreduce, geo.world)
+        self.sym_bytes = self.lib.aar_sym_bytes(geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code, os_cap,
+                                                geo.block_step_arg)
+        self.flag_bytes = self.lib.aar_sym_flag_bytes(geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code,
+                                                      os_cap, geo.block_step_arg)
+        self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
+        self.launches = 0
+
+    def fill(self, a: K.AarLaunch, round_: int, inj: Injection | None) -> None:
+        g = self.geo
+        a.world, a.algo = g.world, self.algo
+        a.in_dtype, a.wire_dtype = self.in_code, self.wire_code
+        a.ctas, a.use_tma = self.ctas, 0
+        a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
+        a.L, a.slot, a.tag = g.slots, round_ % g.slots, round_ + 1
+        a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate
+        a.normalize, a.scale = int(self.normalize), self.scale
+        a.timeout_ns = self.timeout_ns
+        a.mute_mask = 0
+        for r in range(K.MAX_RANKS):
+            a.skip_dest_mask[r] = 0
+            a.delay_ns[r] = 0
+        if inj is not None:
+            a.mute_mask = inj.mute
+            for r, m in inj.skip.items():
+                a.skip_dest_mask[r] = m
+            for r, d in inj.delay_ns.items():
+                a.delay_ns[r] = int(d)
+
+    def launch(self, a: K.AarLaunch, stream: torch.cuda.Stream | None = None) -> int:
+        s = stream if stream is not None else torch.cuda.current_stream()
+        n = K.check(self.lib.aar_allreduce_round(C.byref(a), C.c_void_p(s.cuda_stream)), "aar_allreduce_round")
+        self.launches += n
+        return n
+
+
+class EmulatedCluster:
+    """``world`` virtual ranks on one GPU; every round is ONE cooperative kernel launch."""
+
+    def __init__(self, world: int, n: int, max_chunk: int, max_lag: int = 1, dtype=torch.float32,
+                 wire_dtype=None, th_reduce: float = 1.0, th_complete: float = 1.0,
+                 th_allreduce: float | None = None, ctas: int | None = None, align_blocks: bool = False,
+                 timeout_ms: float = 2000.0, scale: float = 1.0, normalize: bool = False,
+                 device: str | torch.device = "cuda:0"):
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
+        wire = wire_dtype or dtype
+        lib = K.lib()
+        cap = K.check(lib.aar_max_emu_ctas(world, self.device.index or 0), "aar_max_emu_ctas")
+        want = ctas or default_ctas(n * torch.empty((), dtype=dtype).element_size())
+        self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
+                                      max(1, min(want, cap)), timeout_ms, scale, normalize)
+        L = self.launcher
+        self.world = world
+        self.sym = torch.zeros(world, L.sym_bytes, dtype=torch.uint8, device=self.device)
+        self.scratch = torch.zeros(world, L.scratch_bytes, dtype=torch.uint8, device=self.device)
+        self.host_flags = torch.zeros(world * 4, dtype=torch.int32).pin_memory()
+        self.outs = [torch.empty(n, dtype=dtype, device=self.device) for _ in range(world)]
+        self.counts = [torch.empty(n, dtype=torch.int32, device=self.device) for _ in range(world)]
+        self.round = 0
+
+    def run_round(self, srcs, inj: Injection | None = None, outs=None, counts=None, round_: int | None = None,
+                  force: bool = False):
+        """One allreduce round over ``srcs`` (one tensor per virtual rank). Returns (outs, counts)."""
+        r = self.round if round_ is None else round_
+        outs = outs or self.outs
+        counts = counts or self.counts
+        a = K.AarLaunch()
+        self.launcher.fill(a, r, inj)
+        a.rank, a.emu = 0, 1
+        for i in range(self.world):
+            assert srcs[i].numel() == self.geo.n and srcs[i].dtype == self.launcher.dtype and srcs[i].is_contiguous()
+            a.src[i] = srcs[i].data_ptr()
+            a.out[i] = outs[i].data_ptr()
+            a.counts[i] = counts[i].data_ptr()
+            a.sym[i] = self.sym[i].data_ptr()
+            a.scratch[i] = self.scratch[i].data_ptr()
+            self.host_flags[4 * i] = (r + 1) if force else 0
+        a.mc_base = None
+        a.host_flags = self.host_flags.data_ptr()
+        self.launcher.launch(a)
+        if round_ is None:
+            self.round += 1
+        return outs, counts
+
+    def timeouts_seen(self) -> list[int]:
+        torch.cuda.synchronize(self.device)
+        return [int(self.host_flags[4 * i + 2]) for i in range(self.world)]
+
+    def done_tags(self) -> list[int]:
+        torch.cuda.synchronize(self.device)
+        return [int(self.host_flags[4 * i + 1]) for i in range(self.world)]

@@ -1,0 +1,111 @@
+"""DeviceAllreduce: one rank of the fused allreduce on its own GPU.
+
+Owns the rank's slice of the symmetric heap (``csrc/cuda/sym_heap.cu``), its scratch and mapped
+host flags, and launches one fused kernel per round.  The peers are plain device pointers into
+the other ranks' regions, reached over NVLink; no NCCL call is involved anywhere on this path.
+
+Rendezvous needs nothing but a directory every rank can see (unix sockets carry the VMM file
+descriptors), so the engine can be brought up by ``torchrun`` ranks, by workers that got their
+ids from the coordinator, or by hand.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import tempfile
+
+import torch
+
+from ..ops import cuda as K
+from ..ops.fused_allreduce import Injection, RoundLauncher
+from ..ops.geometry import Geometry, default_ctas
+
+
+def default_uds_dir(tag: str | int | None = None) -> str:
+    tag = tag if tag is not None else os.environ.get("MASTER_PORT", "0")
+    d = os.path.join(tempfile.gettempdir(), f"aar_b200_{os.getuid()}_{tag}")
+    os.makedirs(d, exist_ok=True)
+    return d
+
+
+class DeviceAllreduce:
+    def __init__(self, rank: int, world: int, n: int, max_chunk: int, max_lag: int = 1,
+                 dtype: torch.dtype = torch.float32, wire_dtype: torch.dtype | None = None,
+                 th_reduce: float = 1.0, th_complete: float = 1.0, th_allreduce: float | None = None,
+                 device: int | None = None, uds_dir: str | None = None, multicast: bool = True,
+                 align_blocks: bool = True, ctas: int | None = None, timeout_ms: float = 2000.0,
+                 scale: float = 1.0, normalize: bool = False):
+        self.rank, self.world = rank, world
+        self.device_index = torch.cuda.current_device() if device is None else device
+        self.device = torch.device("cuda", self.device_index)
+        torch.cuda.set_device(self.device)
+        self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
+        wire = wire_dtype or dtype
+        elem = torch.empty((), dtype=dtype).element_size()
+        self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
+                                      ctas or default_ctas(n * elem), timeout_ms, scale, normalize)
+        lib = self.launcher.lib
+        self._heap = C.c_void_p()
+        K.check(lib.aar_heap_create(C.byref(self._heap), rank, world, self.device_index, self.launcher.sym_bytes,
+                                    (uds_dir or default_uds_dir()).encode(), int(multicast)), "aar_heap_create")
+        bases = (C.c_void_p * world)()
+        mc = C.c_void_p()
+        K.check(lib.aar_heap_ptrs(self._heap, bases, C.byref(mc)), "aar_heap_ptrs")
+        self.peer_ptrs = [int(bases[i]) for i in range(world)]
+        self.mc_ptr = mc.value  # None when the driver exposes no multicast
+        self.scratch = torch.zeros(self.launcher.scratch_bytes, dtype=torch.uint8, device=self.device)
+        self.host_flags = torch.zeros(4, dtype=torch.int32).pin_memory()
+        self.round = 0
+        self._launch = K.AarLaunch()
+
+    @property
+    def has_multicast(self) -> bool:
+        return bool(self.mc_ptr)
+
+    def allreduce(self, src: torch.Tensor, out: torch.Tensor, counts: torch.Tensor | None = None,
+                  round_: int | None = None, stream: torch.cuda.Stream | None = None,
+                  inj: Injection | None = None) -> None:
+        """Enqueues one round on ``stream``: ``out`` <- sum over the contributing ranks of ``src``,
+        ``counts`` <- contributors per element.  Rounds must be issued in the same order on every rank."""
+        g = self.geo
+        if src.numel() != g.n or out.numel() != g.n:
+            raise ValueError(f"Input data size {src.numel()} is different from initialization time {g.n}!")
+        if src.dtype != self.launcher.dtype or out.dtype != self.launcher.dtype:
+            raise ValueError("dtype differs from the engine's")
+        r = self.round if round_ is None else round_
+        a = self._launch
+        self.launcher.fill(a, r, inj)
+        a.rank, a.emu = self.rank, 0
+        a.src[0] = src.data_ptr()
+        a.out[0] = out.data_ptr()
+        a.counts[0] = counts.data_ptr() if counts is not None else None
+        a.scratch[0] = self.scratch.data_ptr()
+        for i in range(self.world):
+            a.sym[i] = self.peer_ptrs[i]
+        a.mc_base = self.mc_ptr
+        a.host_flags = self.host_flags.data_ptr()
+        self.launcher.launch(a, stream)
+        if round_ is None:
+            self.round += 1
+
+    def force_complete(self, round_: int) -> None:
+        """Host side of the catch-up path: any wait of rounds <= ``round_`` closes immediately."""
+        self.host_flags[0] = round_ + 1
+
+    def last_done_round(self) -> int:
+        return int(self.host_flags[1]) - 1
+
+    def timeouts_seen(self) -> int:
+        return int(self.host_flags[2])
+
+    def close(self) -> None:
+        if self._heap:
+            torch.cuda.synchronize(self.device)
+            self.launcher.lib.aar_heap_destroy(self._heap)
+            self._heap = C.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass

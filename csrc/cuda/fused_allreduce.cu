@@ -1,0 +1,606 @@
+// Fused scatter -> reduce -> broadcast allreduce round for sm_100a, over NVLink peer memory.
+//
+// One launch per rank per round does what the reference spreads over five message handlers:
+//
+//   phase S  scatter     source cast/scale, chunk slices pushed straight into each owner's
+//                        `scat` slot + arrival flag            (AllreduceWorker.scala:212-238,
+//                                                               AllReduceBuffer.scala:25-32)
+//   phase R  reduce      wait for >= int(thReduce*P) arrivals of a chunk, fp32 sum over the
+//                        arrived peers in peer order, contributor count, optional 1/count,
+//                        push into every peer's `sink` slot + reduced flag
+//                                                              (ScatteredDataBuffer.scala:9-32,
+//                                                               AllreduceWorker.scala:177-181,252-268)
+//   phase C  complete    wait for >= int(thComplete*totalChunks) reduced chunks, assemble the
+//                        output and the per-element counts, zeros/count 0 for missing chunks,
+//                        publish CompleteAllreduce             (ReducedDataBuffer.scala:13-66,
+//                                                               AllreduceWorker.scala:270-285)
+//
+// Messages are stores into a peer's symmetric region followed by a release-store of a
+// round-tagged flag; receivers acquire-load the flag.  Differences from the reference that come
+// with polling instead of mailboxes: thresholds fire at "count >= required" with the true count
+// reported (the reference fires at equality), a round may also be closed by a timeout or by the
+// host's force flag (the reference's catch-up, AllreduceWorker.scala:100-106), and a sender
+// skips a peer whose ring slot is still occupied by a round more than maxLag behind.
+//
+// Grid: block 0 of each rank is the control CTA (one warp: polls reduced flags, takes the
+// completion decision); blocks 1..ctas move data.  In emulation mode blockIdx.y is the rank and
+// one cooperative launch runs every rank of the job on one GPU.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+
+#include "aar/device_layout.h"
+#include "aar_b200.h"
+#include "device_utils.cuh"
+
+namespace aar {
+
+constexpr int kThreads = 512;
+constexpr int kUnitsPerThread = 4;
+
+struct KParams {
+  AarLaunch a;
+  SymLayout sym;
+  ScratchLayout scr;
+  Partition part;
+  int tile_elems;     // elements one CTA moves per work item
+  int tpc;            // tiles per full chunk
+  int total_chunks;   // reduced chunks that exist this round (empty trailing blocks excluded)
+  int vec_ok;         // 16-byte paths usable (alignment of pointers, step and chunk size)
+};
+
+struct Ctx {
+  int rank, vr, P, slot;
+  uint32_t tag;
+  uint8_t* my_sym;
+  uint8_t* scratch;
+  volatile uint32_t* host;
+  uint64_t deadline;
+};
+
+__device__ __forceinline__ bool forced(const Ctx& c) { return c.host != nullptr && c.host[0] >= c.tag; }
+__device__ __forceinline__ void note_timeout(const Ctx& c) {
+  if (c.host != nullptr) c.host[2] = c.tag;  // last round closed by a timeout (plain store: host memory)
+}
+
+// ---------------------------------------------------------------- tile movers
+// src (TIn, local) -> dst (TW, possibly a peer), scaled.
+template <typename TIn, typename TW>
+__device__ __forceinline__ void push_tile(const TIn* __restrict__ src, TW* __restrict__ dst, int len, float scale,
+                                          bool vec) {
+  constexpr int E = 16 / (sizeof(TIn) > sizeof(TW) ? sizeof(TIn) : sizeof(TW));
+  using UI = Unit<TIn, E>;
+  using UW = Unit<TW, E>;
+  if (vec) {
+    const int units = len / E;
+    const auto* s = reinterpret_cast<const typename UI::raw_t*>(src);
+    auto* d = reinterpret_cast<typename UW::raw_t*>(dst);
+    for (int u0 = threadIdx.x; u0 < units; u0 += kThreads * kUnitsPerThread) {
+      typename UI::raw_t r[kUnitsPerThread];
+#pragma unroll
+      for (int j = 0; j < kUnitsPerThread; ++j) {
+        const int u = u0 + j * kThreads;
+        if (u < units) r[j] = ld_stream(s + u);
+      }
+#pragma unroll
+      for (int j = 0; j < kUnitsPerThread; ++j) {
+        const int u = u0 + j * kThreads;
+        if (u < units) {
+          float v[E];
+          UI::unpack(r[j], v);
+#pragma unroll
+          for (int e = 0; e < E; ++e) v[e] *= scale;
+          d[u] = UW::pack(v);
+        }
+      }
+    }
+    for (int i = units * E + threadIdx.x; i < len; i += kThreads) dst[i] = from_float<TW>(to_float(src[i]) * scale);
+  } else {
+    for (int i = threadIdx.x; i < len; i += kThreads) dst[i] = from_float<TW>(to_float(src[i]) * scale);
+  }
+}
+
+// Sum of the arrived peers' rows (local, written by peers) -> every peer's sink row.
+template <typename TW>
+__device__ __forceinline__ void reduce_tile(const TW* __restrict__ scat0, int64_t row_stride, uint32_t mask, int P,
+                                            TW* const* __restrict__ dst, int len, float post, bool vec) {
+  constexpr int E = 16 / sizeof(TW);
+  using U = Unit<TW, E>;
+  if (vec) {
+    const int units = len / E;
+    for (int u = threadIdx.x; u < units; u += kThreads) {
+      float acc[E];
+#pragma unroll
+      for (int e = 0; e < E; ++e) acc[e] = 0.f;
+      for (int s0 = 0; s0 < P; s0 += 8) {  // 8 loads in flight, summed in peer order
+        typename U::raw_t r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int s = s0 + j;
+          if (s < P && ((mask >> s) & 1u))
+            r[j] = ld_fresh(reinterpret_cast<const typename U::raw_t*>(scat0 + s * row_stride) + u);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int s = s0 + j;
+          if (s < P && ((mask >> s) & 1u)) {
+            float v[E];
+            U::unpack(r[j], v);
+#pragma unroll
+            for (int e = 0; e < E; ++e) acc[e] += v[e];
+          }
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < E; ++e) acc[e] *= post;
+      const typename U::raw_t out = U::pack(acc);
+      for (int q = 0; q < P; ++q) reinterpret_cast<typename U::raw_t*>(dst[q])[u] = out;
+    }
+    for (int i = units * E + threadIdx.x; i < len; i += kThreads) {
+      float acc = 0.f;
+      for (int s = 0; s < P; ++s)
+        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(scat0 + s * row_stride + i));
+      const TW o = from_float<TW>(acc * post);
+      for (int q = 0; q < P; ++q) dst[q][i] = o;
+    }
+  } else {
+    for (int i = threadIdx.x; i < len; i += kThreads) {
+      float acc = 0.f;
+      for (int s = 0; s < P; ++s)
+        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(scat0 + s * row_stride + i));
+      const TW o = from_float<TW>(acc * post);
+      for (int q = 0; q < P; ++q) dst[q][i] = o;
+    }
+  }
+}
+
+// sink row (local, written by the owner) -> user output + per-element counts.
+template <typename TW, typename TOut>
+__device__ __forceinline__ void flush_tile(const TW* __restrict__ sink, TOut* __restrict__ out,
+                                           int32_t* __restrict__ counts, int len, bool present, int cnt, bool vec) {
+  constexpr int E = 16 / (sizeof(TOut) > sizeof(TW) ? sizeof(TOut) : sizeof(TW));
+  using UW = Unit<TW, E>;
+  using UO = Unit<TOut, E>;
+  if (vec) {
+    const int units = len / E;
+    for (int u0 = threadIdx.x; u0 < units; u0 += kThreads * kUnitsPerThread) {
+      typename UW::raw_t r[kUnitsPerThread];
+      if (present) {
+#pragma unroll
+        for (int j = 0; j < kUnitsPerThread; ++j) {
+          const int u = u0 + j * kThreads;
+          if (u < units) r[j] = ld_fresh(reinterpret_cast<const typename UW::raw_t*>(sink) + u);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < kUnitsPerThread; ++j) {
+        const int u = u0 + j * kThreads;
+        if (u < units) {
+          float v[E];
+          if (present) {
+            UW::unpack(r[j], v);
+          } else {
+#pragma unroll
+            for (int e = 0; e < E; ++e) v[e] = 0.f;
+          }
+          reinterpret_cast<typename UO::raw_t*>(out)[u] = UO::pack(v);
+          if (counts != nullptr) {
+            int4* cp = reinterpret_cast<int4*>(counts + static_cast<int64_t>(u) * E);
+#pragma unroll
+            for (int e = 0; e < E / 4; ++e) cp[e] = make_int4(cnt, cnt, cnt, cnt);
+          }
+        }
+      }
+    }
+    for (int i = units * E + threadIdx.x; i < len; i += kThreads) {
+      out[i] = present ? from_float<TOut>(to_float(ld_fresh_scalar(sink + i))) : from_float<TOut>(0.f);
+      if (counts != nullptr) counts[i] = cnt;
+    }
+  } else {
+    for (int i = threadIdx.x; i < len; i += kThreads) {
+      out[i] = present ? from_float<TOut>(to_float(ld_fresh_scalar(sink + i))) : from_float<TOut>(0.f);
+      if (counts != nullptr) counts[i] = cnt;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- shared decisions
+// Set of peers this launch may push to: a peer whose ring slot still holds a round more than
+// maxLag behind is skipped for the whole launch (first CTA to look decides for all).
+__device__ __forceinline__ uint32_t decide_dest_mask(const KParams& p, const Ctx& c) {
+  uint32_t* word = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_fin_cnt) + 1;
+  uint32_t m = ld_volatile(word);
+  if (m & kDecided) return m & ~kDecided;
+  const uint32_t* done = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_done);
+  uint32_t ok = 0;
+  for (int q = 0; q < c.P; ++q) {
+    const uint32_t d = (q == c.rank) ? c.tag : ld_acquire_sys(done + q);
+    if (d + static_cast<uint32_t>(p.a.L) >= c.tag) ok |= 1u << q;
+  }
+  const uint32_t old = atomicCAS(word, 0u, ok | kDecided);
+  return (old & kDecided) ? (old & ~kDecided) : ok;
+}
+
+// thAllreduce gate: round r may start once `gate_count` peers have finished round r-1
+// (AllreduceMaster.scala:56-62, evaluated on every rank from the replicated `done` flags).
+__device__ __forceinline__ void wait_gate(const KParams& p, const Ctx& c) {
+  if (p.a.gate_count <= 0 || c.tag <= 1) return;
+  const uint32_t* done = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_done);
+  for (;;) {
+    int have = 0;
+    for (int q = 0; q < c.P; ++q) have += (q == c.rank || ld_acquire_sys(done + q) + 1 >= c.tag) ? 1 : 0;
+    if (have >= p.a.gate_count || forced(c)) return;
+    if (globaltimer_ns() > c.deadline) {
+      note_timeout(c);
+      return;
+    }
+    __nanosleep(64);
+  }
+}
+
+// All CTAs of a rank report here; the last one resets the scratch and publishes completion.
+__device__ __forceinline__ void finish_cta(const KParams& p, const Ctx& c) {
+  uint32_t* fin = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_fin_cnt);
+  __threadfence();
+  const uint32_t old = atomicAdd(fin, 1u);
+  if (old != static_cast<uint32_t>(p.a.ctas)) return;  // ctas work CTAs + the control CTA
+  st_volatile(fin, 0u);
+  st_volatile(fin + 1, 0u);
+  uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
+  const int words = (c.P * p.sym.cpb + 31) / 32;
+  for (int i = 0; i < 4 + words; ++i) st_volatile(cw + i, 0u);
+  __threadfence_system();
+  for (int i = 0; i < c.P; ++i) {  // CompleteAllreduce(rank, round) to everyone (AllreduceWorker.scala:276)
+    const int q = (i + c.rank) % c.P;
+    st_release_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + c.rank, c.tag);
+  }
+  if (c.host != nullptr) c.host[1] = c.tag;
+}
+
+// ---------------------------------------------------------------- control CTA
+__device__ void control_cta(const KParams& p, const Ctx& c) {
+  if (threadIdx.x >= 32) return;
+  const int lane = threadIdx.x;
+  const int cpb = p.sym.cpb;
+  const int entries = c.P * cpb;
+  const int words = (entries + 31) / 32;
+  const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + (int64_t)c.slot * entries;
+  uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
+  uint32_t* bitmap = cw + 4;
+  for (;;) {
+    int seen = 0;
+    for (int w = 0; w < words; ++w) {
+      const int idx = w * 32 + lane;
+      bool present = false;
+      if (idx < entries) {
+        const int o = idx / cpb, ch = idx % cpb;
+        if (ch < num_chunks(p.part.size(o), p.a.max_chunk))
+          present = static_cast<uint32_t>(ld_acquire_sys(rflag + idx) >> 32) == c.tag;
+      }
+      const uint32_t m = __ballot_sync(0xffffffffu, present);
+      seen += __popc(m);
+      if (lane == 0) st_volatile(bitmap + w, m);
+    }
+    bool close = seen >= p.a.req_complete || seen >= p.total_chunks;
+    if (!close && lane == 0) {
+      if (forced(c)) close = true;
+      else if (globaltimer_ns() > c.deadline) {
+        note_timeout(c);
+        close = true;
+      }
+    }
+    close = __shfl_sync(0xffffffffu, close ? 1 : 0, 0) != 0 || close;
+    if (close) break;
+    __nanosleep(100);
+  }
+  if (lane == 0) {
+    __threadfence();
+    st_volatile(cw, kDecided);
+    finish_cta(p, c);
+  }
+}
+
+// ---------------------------------------------------------------- work CTAs
+template <typename TIn, typename TW>
+__device__ void work_cta(const KParams& p, const Ctx& c) {
+  __shared__ uint32_t sh_word;
+  __shared__ int sh_cnt;
+  __shared__ TW* sh_dst[kMaxRanks];
+  const int P = c.P;
+  const int cpb = p.sym.cpb;
+  const int tile = p.tile_elems;
+  const int tpc = p.tpc;
+  const int wid = blockIdx.x - 1;
+  const bool vec = p.vec_ok != 0;
+  const TIn* src = static_cast<const TIn*>(p.a.src[c.vr]);
+  TIn* out = static_cast<TIn*>(p.a.out[c.vr]);
+  int32_t* counts = p.a.counts[c.vr];
+  uint32_t* scat_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt);
+  uint32_t* red_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt);
+  uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask);
+
+  if (threadIdx.x == 0) {
+    if (p.a.delay_ns[c.rank] != 0) {  // injected straggler
+      const uint64_t until = globaltimer_ns() + p.a.delay_ns[c.rank];
+      while (globaltimer_ns() < until) __nanosleep(256);
+    }
+    wait_gate(p, c);
+    sh_word = decide_dest_mask(p, c);
+  }
+  __syncthreads();
+  const uint32_t dest_ok = sh_word;
+  const bool muted = (p.a.mute_mask >> c.rank) & 1u;
+  const uint32_t skip = p.a.skip_dest_mask[c.rank];
+  __syncthreads();
+
+  // ---- phase S: scatter my message, chunk-major, destinations rotated from self ----
+  {
+    const int items = cpb * P * tpc;
+    for (int item = wid; item < items; item += p.a.ctas) {
+      const int k = item % tpc;
+      const int d = ((item / tpc) % P + c.rank) % P;
+      const int ch = item / (tpc * P);
+      const int64_t bsize = p.part.size(d);
+      if (ch >= num_chunks(bsize, p.a.max_chunk)) continue;
+      const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
+      const int ntiles = static_cast<int>(ceil_div(ce - cb, tile));
+      if (k >= ntiles) continue;
+      if (muted || ((skip >> d) & 1u) || !((dest_ok >> d) & 1u)) continue;
+      const int64_t off = cb + static_cast<int64_t>(k) * tile;
+      const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
+      TW* dst = reinterpret_cast<TW*>(p.a.sym[d] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off;
+      push_tile<TIn, TW>(src + p.part.start(d) + off, dst, len, p.a.scale, vec);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        uint32_t* cnt = scat_cnt + d * cpb + ch;
+        if (atomicAdd(cnt, 1u) == static_cast<uint32_t>(ntiles - 1)) {  // chunk fully pushed: ScatterBlock sent
+          st_volatile(cnt, 0u);
+          __threadfence_system();
+          st_release_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch),
+                         c.tag);
+        }
+      }
+    }
+  }
+
+  // ---- phase R: reduce my block chunk by chunk and broadcast ----
+  {
+    const int64_t bsize = p.part.size(c.rank);
+    const int nch = num_chunks(bsize, p.a.max_chunk);
+    const uint32_t* arr = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_arr) + p.sym.arr_index(c.slot, 0, 0);
+    const TW* scat0 = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, 0);
+    const int items = nch * tpc;
+    for (int item = wid; item < items; item += p.a.ctas) {
+      const int k = item % tpc;
+      const int ch = item / tpc;
+      const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
+      const int ntiles = static_cast<int>(ceil_div(ce - cb, tile));
+      if (k >= ntiles) continue;
+      const int64_t off = cb + static_cast<int64_t>(k) * tile;
+      const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
+      if (threadIdx.x == 0) {
+        uint32_t m = ld_volatile(red_mask + ch);
+        while (!(m & kDecided)) {
+          uint32_t have = 0;
+          for (int s = 0; s < P; ++s)
+            if (ld_acquire_sys(arr + s * cpb + ch) == c.tag) have |= 1u << s;
+          bool fire = __popc(have) >= p.a.req_reduce || forced(c);
+          if (!fire && globaltimer_ns() > c.deadline) {
+            note_timeout(c);
+            fire = true;
+          }
+          if (fire) {  // first CTA to see the threshold met fixes the contributor set of the chunk
+            const uint32_t old = atomicCAS(red_mask + ch, 0u, have | kDecided);
+            m = (old & kDecided) ? old : (have | kDecided);
+            break;
+          }
+          __nanosleep(32);
+          m = ld_volatile(red_mask + ch);
+        }
+        m &= ~kDecided;
+        for (int s = 0; s < P; ++s)  // acquire every contributor's data on this SM
+          if ((m >> s) & 1u) (void)ld_acquire_sys(arr + s * cpb + ch);
+        sh_word = m;
+      }
+      if (threadIdx.x < P) {
+        const int q = (threadIdx.x + c.rank) % P;
+        TW* base = reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off;
+        // A peer that is skipped this launch gets its copy redirected to my own sink row.
+        sh_dst[threadIdx.x] = ((dest_ok >> q) & 1u)
+                                  ? base
+                                  : reinterpret_cast<TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off;
+      }
+      __syncthreads();
+      const uint32_t mask = sh_word;
+      const int cnt = __popc(mask);
+      const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
+      reduce_tile<TW>(scat0 + off, p.sym.block_pad, mask, P, sh_dst, len, post, vec);
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        if (atomicAdd(red_cnt + ch, 1u) == static_cast<uint32_t>(ntiles - 1)) {  // ReduceBlock sent
+          st_volatile(red_cnt + ch, 0u);
+          st_volatile(red_mask + ch, 0u);
+          __threadfence_system();
+          const uint64_t f = (static_cast<uint64_t>(c.tag) << 32) | static_cast<uint32_t>(cnt);
+          for (int i = 0; i < P; ++i) {
+            const int q = (i + c.rank) % P;
+            if ((dest_ok >> q) & 1u)
+              st_release_sys(reinterpret_cast<uint64_t*>(p.a.sym[q] + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
+          }
+        }
+      }
+    }
+  }
+
+  // ---- phase C: assemble output + counts as reduced chunks are acknowledged ----
+  {
+    const uint32_t* cw = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_complete);
+    const uint32_t* bitmap = cw + 4;
+    const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + p.sym.arr_index(c.slot, 0, 0);
+    const int items = cpb * P * tpc;
+    for (int item = wid; item < items; item += p.a.ctas) {
+      const int k = item % tpc;
+      const int o = ((item / tpc) % P + c.rank) % P;
+      const int ch = item / (tpc * P);
+      const int64_t bsize = p.part.size(o);
+      if (ch >= num_chunks(bsize, p.a.max_chunk)) continue;
+      const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
+      const int ntiles = static_cast<int>(ceil_div(ce - cb, tile));
+      if (k >= ntiles) continue;
+      const int64_t off = cb + static_cast<int64_t>(k) * tile;
+      const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
+      const int idx = o * cpb + ch;
+      if (threadIdx.x == 0) {
+        bool present = false;
+        for (;;) {
+          if ((ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u) {
+            present = true;
+            break;
+          }
+          if (ld_volatile(cw) & kDecided) {  // closed: the snapshot is final
+            present = (ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u;
+            break;
+          }
+          if (globaltimer_ns() > c.deadline + 1000000000ull) {  // the control CTA never answered
+            note_timeout(c);
+            break;
+          }
+          __nanosleep(64);
+        }
+        int cnt = 0;
+        if (present) cnt = static_cast<int>(static_cast<uint32_t>(ld_acquire_sys(rflag + idx)));
+        sh_word = present ? 1u : 0u;
+        sh_cnt = cnt;
+      }
+      __syncthreads();
+      const bool present = sh_word != 0;
+      const int cnt = sh_cnt;
+      const TW* sink = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, o) + off;
+      const int64_t g = p.part.start(o) + off;
+      flush_tile<TW, TIn>(sink, out + g, counts != nullptr ? counts + g : nullptr, len, present, cnt, vec);
+      __syncthreads();
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) finish_cta(p, c);
+}
+
+template <typename TIn, typename TW>
+__global__ void __launch_bounds__(kThreads, 1) aar_twoshot_kernel(const __grid_constant__ KParams p) {
+  Ctx c;
+  c.vr = p.a.emu ? blockIdx.y : 0;
+  c.rank = p.a.emu ? static_cast<int>(blockIdx.y) : p.a.rank;
+  c.P = p.a.world;
+  c.slot = p.a.slot;
+  c.tag = p.a.tag;
+  c.my_sym = p.a.sym[c.rank];
+  c.scratch = p.a.scratch[c.vr];
+  c.host = p.a.host_flags != nullptr ? p.a.host_flags + 4 * c.vr : nullptr;
+  c.deadline = globaltimer_ns() + p.a.timeout_ns;
+  if (blockIdx.x == 0) control_cta(p, c);
+  else work_cta<TIn, TW>(p, c);
+}
+
+// ---------------------------------------------------------------- host side
+thread_local std::string g_error;
+int fail(int code, const std::string& what) {
+  g_error = what;
+  return code;
+}
+
+template <typename TIn, typename TW>
+int launch_twoshot(const KParams& kp, cudaStream_t stream) {
+  dim3 grid(kp.a.ctas + 1, kp.a.emu ? kp.a.world : 1);
+  cudaError_t e;
+  if (kp.a.emu) {
+    void* args[] = {const_cast<KParams*>(&kp)};
+    e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(aar_twoshot_kernel<TIn, TW>), grid, dim3(kThreads), args, 0,
+                                    stream);
+  } else {
+    aar_twoshot_kernel<TIn, TW><<<grid, kThreads, 0, stream>>>(kp);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("two-shot launch: ") + cudaGetErrorString(e));
+  return 1;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+}  // namespace aar
+
+using namespace aar;
+
+extern "C" {
+
+const char* aar_last_error(void) { return g_error.c_str(); }
+
+static int wire_bytes_of(int dtype) { return dtype == AAR_BF16 ? 2 : 4; }
+
+int64_t aar_sym_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                      int64_t block_step) {
+  return SymLayout::make(n, max_chunk, world, L, wire_bytes_of(wire_dtype), os_cap, block_step).total_bytes;
+}
+int64_t aar_sym_flag_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                           int64_t block_step) {
+  return SymLayout::make(n, max_chunk, world, L, wire_bytes_of(wire_dtype), os_cap, block_step).flags_bytes();
+}
+int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block_step) {
+  const SymLayout s = SymLayout::make(n, max_chunk, world, 1, 4, 0, block_step);
+  return ScratchLayout::make(world, s.cpb).total_bytes;
+}
+
+int aar_max_emu_ctas(int world, int device) {
+  int sms = 0, per_sm = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return AAR_ECUDA;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, aar_twoshot_kernel<float, float>, kThreads, 0) != cudaSuccess)
+    return AAR_ECUDA;
+  const int resident = sms * (per_sm > 0 ? per_sm : 1);
+  return resident / world - 1;
+}
+
+int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
+  if (a == nullptr) return fail(AAR_EINVAL, "null launch");
+  if (a->world < 1 || a->world > AAR_MAX_RANKS) return fail(AAR_EINVAL, "world must be 1..16");
+  if (a->n <= 0 || a->max_chunk <= 0 || a->L < 1 || a->ctas < 1) return fail(AAR_EINVAL, "bad size/ring/cta arguments");
+  if (a->tag == 0) return fail(AAR_EINVAL, "tag is round+1 and must be > 0");
+  if (a->block_step != 0 && a->block_step * a->world < a->n) return fail(AAR_EINVAL, "block_step too small");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  KParams kp;
+  kp.a = *a;
+  const int wb = wire_bytes_of(a->wire_dtype);
+  kp.sym = SymLayout::make(a->n, a->max_chunk, a->world, a->L, wb, a->os_cap, a->block_step);
+  kp.scr = ScratchLayout::make(a->world, kp.sym.cpb);
+  kp.part = Partition(a->n, a->world, kp.sym.block);
+  kp.total_chunks = total_reduced_chunks(kp.part, a->max_chunk);
+  const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
+  const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);
+  kp.tile_elems = kThreads * kUnitsPerThread * unit_elems;
+  kp.tpc = static_cast<int>(ceil_div(a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1),
+                                     kp.tile_elems));
+  if (kp.tpc < 1) kp.tpc = 1;
+  // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
+  const int64_t align_elems = 16 / (in_bytes < wb ? in_bytes : wb);
+  bool vec = (kp.sym.block % align_elems == 0) && (a->max_chunk % align_elems == 0 || a->max_chunk >= kp.sym.block);
+  const int ranks_here = a->emu ? a->world : 1;
+  for (int r = 0; r < ranks_here; ++r) {
+    if (a->src[r] == nullptr || a->out[r] == nullptr || a->scratch[r] == nullptr)
+      return fail(AAR_EINVAL, "src/out/scratch pointer missing");
+    vec = vec && aligned16(a->src[r]) && aligned16(a->out[r]) && (a->counts[r] == nullptr || aligned16(a->counts[r]));
+  }
+  for (int r = 0; r < a->world; ++r)
+    if (a->sym[r] == nullptr) return fail(AAR_EINVAL, "symmetric base pointer missing");
+  kp.vec_ok = vec ? 1 : 0;
+
+  if (a->algo != AAR_ALGO_TWOSHOT) return fail(AAR_EUNSUPPORTED, "algorithm not built into this library yet");
+  if (a->in_dtype == AAR_F32 && a->wire_dtype == AAR_F32) return launch_twoshot<float, float>(kp, stream);
+  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_twoshot<__nv_bfloat16, __nv_bfloat16>(kp, stream);
+  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_F32) return launch_twoshot<__nv_bfloat16, float>(kp, stream);
+  return fail(AAR_EUNSUPPORTED, "dtype combination not supported (f32/f32, bf16/bf16, bf16/f32)");
+}
+
+}  // extern "C"

@@ -46,6 +46,9 @@ struct Partition {
 
   AAR_HD Partition() : n(0), P(0), step(0) {}
   AAR_HD Partition(int64_t n_, int P_) : n(n_), P(P_), step(P_ > 0 ? ceil_div(n_, P_) : 0) {}
+  // Explicit step >= ceil(n/P): the device path may round blocks up to an alignment unit
+  // (trailing owners then hold short or empty blocks).
+  AAR_HD Partition(int64_t n_, int P_, int64_t step_) : n(n_), P(P_), step(step_) {}
 
   AAR_HD int64_t start(int i) const {
     int64_t s = static_cast<int64_t>(i) * step;

@@ -1,0 +1,89 @@
+/* C ABI of libaar_cuda.so — the sm_100a data plane of akka_allreduce_b200.
+ *
+ * Everything here is callable from C, ctypes or a torch extension.  Functions return 0 on
+ * success or a negative AAR_E* code; aar_last_error() gives the text of the last failure on
+ * the calling thread.  Nothing in this header allocates device memory unless it says so.
+ */
+#ifndef AAR_B200_H_
+#define AAR_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AAR_MAX_RANKS 16
+
+enum { AAR_OK = 0, AAR_EINVAL = -1, AAR_ECUDA = -2, AAR_EUNSUPPORTED = -3, AAR_ETOOBIG = -4 };
+enum { AAR_F32 = 0, AAR_BF16 = 1 };
+enum { AAR_ALGO_TWOSHOT = 0, AAR_ALGO_ONESHOT = 1, AAR_ALGO_NVLS = 2 };
+
+/* One fused scatter -> reduce -> broadcast round (reference hot path: AllreduceWorker.scala:
+ * 212-238 scatter, ScatteredDataBuffer.scala:20-32 reduce, AllreduceWorker.scala:252-268
+ * broadcast, ReducedDataBuffer.scala:26-53 flush).  In emulation mode (`emu` != 0) one
+ * cooperative launch plays all `world` ranks on one GPU: rank = blockIdx.y, and src/out/
+ * counts/sym/scratch are indexed by rank.  In real mode only index 0 of src/out/counts/
+ * scratch is used and sym[] holds the peer-mapped bases of every rank's region. */
+typedef struct AarLaunch {
+  int32_t rank, world, emu;
+  int32_t algo;             /* AAR_ALGO_* */
+  int32_t in_dtype;         /* dtype of src and out: AAR_F32 | AAR_BF16 */
+  int32_t wire_dtype;       /* dtype of the symmetric slots */
+  int32_t ctas;             /* work CTAs per rank (one control CTA is added) */
+  int32_t use_tma;          /* stage tiles with cp.async.bulk when alignment allows */
+  int64_t n, max_chunk;     /* dataSize, maxChunkSize (elements) */
+  int64_t os_cap;           /* one-shot capacity the region was laid out with */
+  int64_t block_step;       /* 0 = reference partition ceil(n/world); else an aligned step >= that */
+  int32_t L, slot;          /* ring slots (maxLag+1), round % L */
+  uint32_t tag;             /* round + 1 */
+  int32_t req_reduce;       /* int(thReduce * P) */
+  int32_t req_complete;     /* int(thComplete * totalChunks) */
+  int32_t gate_count;       /* peers that must have finished round-1 before scattering; 0 = no gate */
+  int32_t normalize;        /* divide every chunk by its contributor count */
+  float scale;              /* source scale fused into the scatter */
+  uint32_t skip_dest_mask[AAR_MAX_RANKS]; /* straggler injection: rank r does not scatter to these dests */
+  uint32_t mute_mask;       /* straggler injection: these ranks do not scatter at all this round */
+  uint64_t delay_ns[AAR_MAX_RANKS];       /* straggler injection: rank r idles this long first */
+  uint64_t timeout_ns;      /* bound on every flag wait; on expiry the round is force-completed */
+  const void* src[AAR_MAX_RANKS];
+  void* out[AAR_MAX_RANKS];          /* dataSize elements of in_dtype */
+  int32_t* counts[AAR_MAX_RANKS];    /* dataSize int32 contributor counts, or NULL */
+  uint8_t* sym[AAR_MAX_RANKS];       /* base of every rank's symmetric region */
+  uint8_t* mc_base;                  /* NVLS multicast alias of the region, or NULL */
+  uint8_t* scratch[AAR_MAX_RANKS];   /* local scratch, aar_scratch_bytes(), zeroed once */
+  volatile uint32_t* host_flags;     /* mapped pinned: [0] force-complete tag (read), [1] done tag,
+                                        [2] timeouts seen (written); 4 words per rank in emulation
+                                        mode; may be NULL */
+} AarLaunch;
+
+/* Sizes of the symmetric region / local scratch for a configuration. */
+int64_t aar_sym_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                      int64_t block_step);
+int64_t aar_sym_flag_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                           int64_t block_step);
+int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block_step);
+
+/* Launches one round on `stream` (a cudaStream_t).  Returns the number of kernels launched
+ * (>0) or a negative error. */
+int aar_allreduce_round(const AarLaunch* launch, void* stream);
+
+/* Co-residency limit for emulation mode: max work CTAs per rank so that world*(ctas+1) blocks fit. */
+int aar_max_emu_ctas(int world, int device);
+
+/* Symmetric heap (csrc/cuda/sym_heap.cu): CUDA VMM allocation shared with every peer process
+ * through POSIX file descriptors passed over unix sockets, plus an NVLS multicast alias when
+ * the driver supports it.  `uds_dir` must be a directory all ranks can reach. */
+typedef struct AarHeap AarHeap;
+int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t bytes, const char* uds_dir,
+                    int want_multicast);
+int aar_heap_ptrs(AarHeap* h, uint8_t** peer_bases /* [world] */, uint8_t** mc_base);
+int64_t aar_heap_bytes(AarHeap* h);
+int aar_heap_destroy(AarHeap* h);
+
+const char* aar_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AAR_B200_H_ */

@@ -1,0 +1,206 @@
+"""The fused sm_100a kernel, all ranks emulated on one GPU (one cooperative launch per round).
+
+Numerics are checked against a plain PyTorch fp32 reference of the same op (sum over the ranks
+named by ``count``), and against the reference's semantics for partial rounds: output equals the
+sum over exactly ``count`` contributors, zeros where ``count == 0``.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _cluster(*a, **kw):
+    from akka_allreduce_b200.ops.fused_allreduce import EmulatedCluster
+
+    return EmulatedCluster(*a, **kw)
+
+
+def _srcs(world, n, dtype, r, dev="cuda:0"):
+    g = torch.Generator(device="cpu").manual_seed(1000 * r + world)
+    return [torch.randn(n, generator=g, dtype=torch.float32).to(dtype).to(dev) for _ in range(world)]
+
+
+def _ref_sum(srcs, ranks=None):
+    ranks = range(len(srcs)) if ranks is None else ranks
+    acc = torch.zeros_like(srcs[0], dtype=torch.float32)
+    for i in ranks:  # fixed peer order, fp32 accumulate: same order as the kernel
+        acc += srcs[i].float()
+    return acc
+
+
+@pytest.mark.parametrize("world,n,mc,max_lag", [
+    (2, 10, 2, 1),            # BASELINE config 1 shape
+    (4, 778, 3, 3),           # scripts/testAllreduceMaster.sc shape (scalar path, uneven tail)
+    (3, 9, 2, 5),
+    (4, 9, 2, 1),             # empty trailing block
+    (8, 1 << 20, 1 << 14, 1),  # vector path, 8 chunks per block
+    (8, 1 << 18, 1 << 18, 2),  # one chunk per block
+    (5, 100003, 4096, 2),     # odd everything
+])
+def test_thresholds_one_matches_fp32_sum(world, n, mc, max_lag):
+    cl = _cluster(world, n, mc, max_lag=max_lag, timeout_ms=5000)
+    for r in range(2 * (max_lag + 1) + 1):  # wraps the lag ring twice
+        srcs = _srcs(world, n, torch.float32, r)
+        outs, counts = cl.run_round(srcs)
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i], want), f"round {r} rank {i}: max err {(outs[i] - want).abs().max()}"
+            assert bool((counts[i] == world).all())
+    assert cl.timeouts_seen() == [0] * world
+    assert cl.done_tags() == [cl.round] * world
+
+
+def test_assert_multiple_ramp():
+    """AllreduceWorker.scala:324-343: ramp source, output == input*k and count == k."""
+    world, n = 4, 778
+    cl = _cluster(world, n, 3, max_lag=3)
+    ramp = torch.arange(n, dtype=torch.float32, device="cuda:0")
+    for _ in range(10):
+        outs, counts = cl.run_round([ramp] * world)
+    for i in range(world):
+        assert torch.equal(outs[i], ramp * world) and bool((counts[i] == world).all())
+
+
+@pytest.mark.parametrize("wire", [torch.bfloat16, torch.float32])
+def test_bf16_source(wire):
+    world, n = 8, 1 << 19
+    cl = _cluster(world, n, 1 << 15, dtype=torch.bfloat16, wire_dtype=wire, align_blocks=True)
+    srcs = _srcs(world, n, torch.bfloat16, 3)
+    outs, counts = cl.run_round(srcs)
+    want = _ref_sum(srcs)
+    for i in range(world):
+        # bf16 output of an fp32 accumulation: one rounding of the result
+        torch.testing.assert_close(outs[i].float(), want, rtol=2 ** -7, atol=1e-2)
+        assert bool((counts[i] == world).all())
+    # every rank holds bit-identical output (one owner reduces each chunk)
+    assert all(torch.equal(outs[0], outs[i]) for i in range(1, world))
+
+
+def test_scale_and_normalize():
+    world, n = 4, 4096
+    cl = _cluster(world, n, 512, scale=0.5, normalize=True)
+    srcs = _srcs(world, n, torch.float32, 7)
+    outs, _ = cl.run_round(srcs)
+    want = sum((s * 0.5 for s in srcs[1:]), srcs[0] * 0.5) / world
+    torch.testing.assert_close(outs[2], want, rtol=1e-6, atol=1e-6)
+
+
+def test_scatter_threshold_with_muted_rank():
+    """thReduce 0.75 of 4: a rank that never scatters is absorbed; count reports 3 contributors."""
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    world, n = 4, 1 << 16
+    cl = _cluster(world, n, 1 << 12, th_reduce=0.75, th_complete=1.0, max_lag=2)
+    for r in range(4):
+        srcs = _srcs(world, n, torch.float32, r)
+        outs, counts = cl.run_round(srcs, Injection(mute=1 << 3))
+        want = _ref_sum(srcs, ranks=[0, 1, 2])
+        for i in range(world):
+            assert torch.equal(outs[i], want) and bool((counts[i] == 3).all())
+    assert cl.timeouts_seen() == [0] * world
+
+
+def test_dropped_scatter_to_one_destination():
+    """Rank 1 drops its ScatterBlocks to rank 2 only: block 2 is closed by the bounded wait with 3
+    contributors, the rest has 4.  (Thresholds stay at 1 so the contributor sets are deterministic: with
+    thReduce < 1 a chunk fires on the first poll that sees enough arrivals.)"""
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    world, n = 4, 4000
+    cl = _cluster(world, n, 256, timeout_ms=20)
+    srcs = _srcs(world, n, torch.float32, 11)
+    outs, counts = cl.run_round(srcs, Injection(skip={1: 1 << 2}))
+    full, part = _ref_sum(srcs), _ref_sum(srcs, ranks=[0, 2, 3])
+    lo, hi = cl.geo.start(2), cl.geo.end(2)
+    for i in range(world):
+        assert torch.equal(outs[i][:lo], full[:lo]) and torch.equal(outs[i][hi:], full[hi:])
+        assert torch.equal(outs[i][lo:hi], part[lo:hi])
+        assert bool((counts[i][lo:hi] == 3).all()) and bool((counts[i][:lo] == 4).all())
+
+
+def test_completion_threshold_with_straggling_owner():
+    """thComplete 0.75: a rank that starts 30 ms late misses the round on the other ranks — its block
+    comes out as zeros with count 0 there (ReducedDataBuffer.scala:26-53), the others' blocks with
+    count 3 (its scatter was late too)."""
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    world, n = 4, 1 << 14
+    cl = _cluster(world, n, 1 << 10, th_reduce=0.75, th_complete=0.75, timeout_ms=5000)
+    srcs = _srcs(world, n, torch.float32, 5)
+    outs, counts = cl.run_round(srcs, Injection(delay_ns={3: 30_000_000}))
+    part = _ref_sum(srcs, ranks=[0, 1, 2])
+    lo = cl.geo.start(3)
+    for i in range(3):
+        assert torch.equal(outs[i][:lo], part[:lo]) and bool((counts[i][:lo] == 3).all())
+        assert bool((outs[i][lo:] == 0).all()) and bool((counts[i][lo:] == 0).all())
+    # the straggler itself: the others' blocks were reduced without it (3); its own block fires on the
+    # first poll that sees >= 3 arrivals, which may or may not include its own contribution yet
+    assert bool((counts[3][:lo] == 3).all()) and torch.equal(outs[3][:lo], part[:lo])
+    own = counts[3][lo:]
+    assert bool(((own == 3) | (own == 4)).all())
+    full = _ref_sum(srcs)
+    assert torch.equal(torch.where(own == 4, full[lo:], part[lo:]), outs[3][lo:])
+    assert cl.timeouts_seen() == [0] * world
+
+
+def test_timeout_force_completes_like_catch_up():
+    """Thresholds 1 and a rank that never scatters: the wait is bounded, the round is closed with what
+    arrived (count 3) — the device form of the catch-up path (AllreduceWorker.scala:100-106)."""
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    world, n = 4, 1 << 12
+    cl = _cluster(world, n, 1 << 10, timeout_ms=20)
+    srcs = _srcs(world, n, torch.float32, 9)
+    outs, counts = cl.run_round(srcs, Injection(mute=1 << 0))
+    want = _ref_sum(srcs, ranks=[1, 2, 3])
+    for i in range(world):
+        assert torch.equal(outs[i], want) and bool((counts[i] == 3).all())
+    assert any(t > 0 for t in cl.timeouts_seen())
+    # the next round is healthy again: scratch and flags were left consistent
+    srcs = _srcs(world, n, torch.float32, 10)
+    outs, counts = cl.run_round(srcs)
+    assert torch.equal(outs[1], _ref_sum(srcs)) and bool((counts[1] == 4).all())
+
+
+def test_host_force_flag_closes_round_immediately():
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    world, n = 4, 1 << 12
+    cl = _cluster(world, n, 1 << 10, timeout_ms=10_000)
+    srcs = _srcs(world, n, torch.float32, 12)
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    outs, counts = cl.run_round(srcs, Injection(mute=1 << 2), force=True)
+    t1.record()
+    torch.cuda.synchronize()
+    assert t0.elapsed_time(t1) < 2000  # did not sit out the 10 s timeout
+    for i in range(world):
+        got = counts[i] > 0
+        assert bool((counts[i][got] <= 4).all())
+
+
+def test_matches_host_engine_oracle():
+    """Same inputs through the C++ host protocol engine (CPU oracle) and the kernel."""
+    from akka_allreduce_b200 import host as h
+
+    world, n, mc = 4, 103, 5
+    rng = np.random.default_rng(0)
+    data = [rng.integers(-50, 50, n).astype(np.float32) for _ in range(world)]
+    bus = h.LocalBus()
+    cfg = h.MasterConfig()
+    cfg.total_workers, cfg.data_size, cfg.max_chunk_size, cfg.max_round, cfg.max_lag = world, n, mc, 0, 1
+    cfg.th_allreduce = cfg.th_reduce = cfg.th_complete = 1.0
+    _, master = bus.add_master(cfg)
+    got = {}
+    for i in range(world):
+        ep, _w = bus.add_worker(lambda it, i=i: data[i], lambda d, c, it, i=i: got.__setitem__(i, (d.copy(), c.copy())))
+        master.member_up(ep)
+    bus.run()
+    cl = _cluster(world, n, mc)
+    outs, counts = cl.run_round([torch.from_numpy(d).cuda() for d in data])
+    for i in range(world):
+        assert np.array_equal(outs[i].cpu().numpy(), got[i][0])
+        assert np.array_equal(counts[i].cpu().numpy(), got[i][1])
