@@ -53,13 +53,14 @@ class RoundLauncher:
         self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.launches = 0
 
-    def fill(self, a: K.AarLaunch, round_: int, inj: Injection | None) -> None:
+    def prepare(self, a: K.AarLaunch) -> None:
+        """Fills everything that does not change from round to round (done once per launch struct)."""
         g = self.geo
         a.world, a.algo = g.world, self.algo
         a.in_dtype, a.wire_dtype = self.in_code, self.wire_code
         a.ctas, a.use_tma = self.ctas, 0
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
-        a.L, a.slot, a.tag = g.slots, round_ % g.slots, round_ + 1
+        a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate
         a.normalize, a.scale = int(self.normalize), self.scale
         a.timeout_ns = self.timeout_ns
@@ -67,12 +68,26 @@ class RoundLauncher:
         for r in range(K.MAX_RANKS):
             a.skip_dest_mask[r] = 0
             a.delay_ns[r] = 0
-        if inj is not None:
-            a.mute_mask = inj.mute
-            for r, m in inj.skip.items():
-                a.skip_dest_mask[r] = m
-            for r, d in inj.delay_ns.items():
-                a.delay_ns[r] = int(d)
+        a._aar_prepared = True
+        a._aar_injected = False
+
+    def fill(self, a: K.AarLaunch, round_: int, inj: Injection | None) -> None:
+        """Per-round fields only: ring slot, round tag and (rarely) the straggler injection."""
+        if not getattr(a, "_aar_prepared", False):
+            self.prepare(a)
+        a.slot, a.tag = round_ % self.geo.slots, round_ + 1
+        if inj is not None or a._aar_injected:
+            a.mute_mask = 0
+            for r in range(K.MAX_RANKS):
+                a.skip_dest_mask[r] = 0
+                a.delay_ns[r] = 0
+            a._aar_injected = inj is not None
+            if inj is not None:
+                a.mute_mask = inj.mute
+                for r, m in inj.skip.items():
+                    a.skip_dest_mask[r] = m
+                for r, d in inj.delay_ns.items():
+                    a.delay_ns[r] = int(d)
 
     def launch(self, a: K.AarLaunch, stream: torch.cuda.Stream | None = None) -> int:
         s = stream if stream is not None else torch.cuda.current_stream()
@@ -106,6 +121,16 @@ class EmulatedCluster:
         self.outs = [torch.empty(n, dtype=dtype, device=self.device) for _ in range(world)]
         self.counts = [torch.empty(n, dtype=torch.int32, device=self.device) for _ in range(world)]
         self.round = 0
+        self._forced = False
+        self._a = K.AarLaunch()
+        self.launcher.prepare(self._a)
+        a = self._a
+        a.rank, a.emu = 0, 1
+        for i in range(world):
+            a.sym[i] = self.sym[i].data_ptr()
+            a.scratch[i] = self.scratch[i].data_ptr()
+        a.mc_base = None
+        a.host_flags = self.host_flags.data_ptr()
 
     def run_round(self, srcs, inj: Injection | None = None, outs=None, counts=None, round_: int | None = None,
                   force: bool = False):
@@ -113,19 +138,17 @@ class EmulatedCluster:
         r = self.round if round_ is None else round_
         outs = outs or self.outs
         counts = counts or self.counts
-        a = K.AarLaunch()
+        a = self._a
         self.launcher.fill(a, r, inj)
-        a.rank, a.emu = 0, 1
         for i in range(self.world):
             assert srcs[i].numel() == self.geo.n and srcs[i].dtype == self.launcher.dtype and srcs[i].is_contiguous()
             a.src[i] = srcs[i].data_ptr()
             a.out[i] = outs[i].data_ptr()
             a.counts[i] = counts[i].data_ptr()
-            a.sym[i] = self.sym[i].data_ptr()
-            a.scratch[i] = self.scratch[i].data_ptr()
-            self.host_flags[4 * i] = (r + 1) if force else 0
-        a.mc_base = None
-        a.host_flags = self.host_flags.data_ptr()
+        if force or self._forced:
+            for i in range(self.world):
+                self.host_flags[4 * i] = (r + 1) if force else 0
+            self._forced = force
         self.launcher.launch(a)
         if round_ is None:
             self.round += 1

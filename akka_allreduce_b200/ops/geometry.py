@@ -87,4 +87,4 @@ def default_ctas(message_bytes: int) -> int:
         return 16
     if message_bytes <= 16 << 20:
         return 32
-    return 64
+    return 96

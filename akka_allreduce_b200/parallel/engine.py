@@ -56,7 +56,14 @@ class DeviceAllreduce:
         self.scratch = torch.zeros(self.launcher.scratch_bytes, dtype=torch.uint8, device=self.device)
         self.host_flags = torch.zeros(4, dtype=torch.int32).pin_memory()
         self.round = 0
-        self._launch = K.AarLaunch()
+        self._launch = a = K.AarLaunch()
+        self.launcher.prepare(a)
+        a.rank, a.emu = rank, 0
+        a.scratch[0] = self.scratch.data_ptr()
+        for i in range(world):
+            a.sym[i] = self.peer_ptrs[i]
+        a.mc_base = self.mc_ptr
+        a.host_flags = self.host_flags.data_ptr()
 
     @property
     def has_multicast(self) -> bool:
@@ -75,15 +82,9 @@ class DeviceAllreduce:
         r = self.round if round_ is None else round_
         a = self._launch
         self.launcher.fill(a, r, inj)
-        a.rank, a.emu = self.rank, 0
         a.src[0] = src.data_ptr()
         a.out[0] = out.data_ptr()
         a.counts[0] = counts.data_ptr() if counts is not None else None
-        a.scratch[0] = self.scratch.data_ptr()
-        for i in range(self.world):
-            a.sym[i] = self.peer_ptrs[i]
-        a.mc_base = self.mc_ptr
-        a.host_flags = self.host_flags.data_ptr()
         self.launcher.launch(a, stream)
         if round_ is None:
             self.round += 1

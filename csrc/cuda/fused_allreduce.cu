@@ -46,8 +46,8 @@ struct KParams {
   SymLayout sym;
   ScratchLayout scr;
   Partition part;
-  int tile_elems;     // elements one CTA moves per work item
-  int tpc;            // tiles per full chunk
+  int part_s, tpc_s;  // scatter/complete phases: elements per work item, items per full chunk
+  int part_r, tpc_r;  // reduce phase: elements per work item, items per full chunk
   int total_chunks;   // reduced chunks that exist this round (empty trailing blocks excluded)
   int vec_ok;         // 16-byte paths usable (alignment of pointers, step and chunk size)
 };
@@ -104,56 +104,75 @@ __device__ __forceinline__ void push_tile(const TIn* __restrict__ src, TW* __res
 }
 
 // Sum of the arrived peers' rows (local, written by peers) -> every peer's sink row.
+// B units per thread per sweep and 8/B peers per load batch: eight 16-byte loads in flight per thread
+// whatever the peer count; every element is still accumulated in peer order 0..P-1.
+template <typename TW, int B>
+__device__ __forceinline__ void reduce_units(const TW* __restrict__ scat0, int64_t row_stride, uint32_t mask, int P,
+                                             TW* const* __restrict__ dst, int units, float post) {
+  constexpr int E = 16 / sizeof(TW);
+  constexpr int PB = 8 / B;
+  using U = Unit<TW, E>;
+  using raw_t = typename U::raw_t;
+  for (int u0 = threadIdx.x; u0 < units; u0 += kThreads * B) {
+    float acc[B][E];
+#pragma unroll
+    for (int b = 0; b < B; ++b)
+#pragma unroll
+      for (int e = 0; e < E; ++e) acc[b][e] = 0.f;
+    for (int s0 = 0; s0 < P; s0 += PB) {
+      raw_t r[B][PB];
+#pragma unroll
+      for (int b = 0; b < B; ++b)
+#pragma unroll
+        for (int j = 0; j < PB; ++j) {
+          const int u = u0 + b * kThreads, s = s0 + j;
+          if (u < units && s < P && ((mask >> s) & 1u))
+            r[b][j] = ld_fresh(reinterpret_cast<const raw_t*>(scat0 + s * row_stride) + u);
+        }
+#pragma unroll
+      for (int b = 0; b < B; ++b)
+#pragma unroll
+        for (int j = 0; j < PB; ++j) {
+          const int u = u0 + b * kThreads, s = s0 + j;
+          if (u < units && s < P && ((mask >> s) & 1u)) {
+            float v[E];
+            U::unpack(r[b][j], v);
+#pragma unroll
+            for (int e = 0; e < E; ++e) acc[b][e] += v[e];
+          }
+        }
+    }
+#pragma unroll
+    for (int b = 0; b < B; ++b) {
+      const int u = u0 + b * kThreads;
+      if (u < units) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[b][e] *= post;
+        const raw_t out = U::pack(acc[b]);
+        for (int q = 0; q < P; ++q) reinterpret_cast<raw_t*>(dst[q])[u] = out;
+      }
+    }
+  }
+}
+
 template <typename TW>
 __device__ __forceinline__ void reduce_tile(const TW* __restrict__ scat0, int64_t row_stride, uint32_t mask, int P,
                                             TW* const* __restrict__ dst, int len, float post, bool vec) {
   constexpr int E = 16 / sizeof(TW);
-  using U = Unit<TW, E>;
+  int done = 0;
   if (vec) {
     const int units = len / E;
-    for (int u = threadIdx.x; u < units; u += kThreads) {
-      float acc[E];
-#pragma unroll
-      for (int e = 0; e < E; ++e) acc[e] = 0.f;
-      for (int s0 = 0; s0 < P; s0 += 8) {  // 8 loads in flight, summed in peer order
-        typename U::raw_t r[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int s = s0 + j;
-          if (s < P && ((mask >> s) & 1u))
-            r[j] = ld_fresh(reinterpret_cast<const typename U::raw_t*>(scat0 + s * row_stride) + u);
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const int s = s0 + j;
-          if (s < P && ((mask >> s) & 1u)) {
-            float v[E];
-            U::unpack(r[j], v);
-#pragma unroll
-            for (int e = 0; e < E; ++e) acc[e] += v[e];
-          }
-        }
-      }
-#pragma unroll
-      for (int e = 0; e < E; ++e) acc[e] *= post;
-      const typename U::raw_t out = U::pack(acc);
-      for (int q = 0; q < P; ++q) reinterpret_cast<typename U::raw_t*>(dst[q])[u] = out;
-    }
-    for (int i = units * E + threadIdx.x; i < len; i += kThreads) {
-      float acc = 0.f;
-      for (int s = 0; s < P; ++s)
-        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(scat0 + s * row_stride + i));
-      const TW o = from_float<TW>(acc * post);
-      for (int q = 0; q < P; ++q) dst[q][i] = o;
-    }
-  } else {
-    for (int i = threadIdx.x; i < len; i += kThreads) {
-      float acc = 0.f;
-      for (int s = 0; s < P; ++s)
-        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(scat0 + s * row_stride + i));
-      const TW o = from_float<TW>(acc * post);
-      for (int q = 0; q < P; ++q) dst[q][i] = o;
-    }
+    if (P <= 2) reduce_units<TW, 4>(scat0, row_stride, mask, P, dst, units, post);
+    else if (P <= 4) reduce_units<TW, 2>(scat0, row_stride, mask, P, dst, units, post);
+    else reduce_units<TW, 1>(scat0, row_stride, mask, P, dst, units, post);
+    done = units * E;
+  }
+  for (int i = done + threadIdx.x; i < len; i += kThreads) {
+    float acc = 0.f;
+    for (int s = 0; s < P; ++s)
+      if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(scat0 + s * row_stride + i));
+    const TW o = from_float<TW>(acc * post);
+    for (int q = 0; q < P; ++q) dst[q][i] = o;
   }
 }
 
@@ -287,8 +306,8 @@ __device__ void control_cta(const KParams& p, const Ctx& c) {
     bool close = seen >= p.a.req_complete || seen >= p.total_chunks;
     if (!close && lane == 0) {
       if (forced(c)) close = true;
-      else if (globaltimer_ns() > c.deadline) {
-        note_timeout(c);
+      else if (globaltimer_ns() > c.deadline + p.a.timeout_ns) {  // owners get one timeout to reduce, the
+        note_timeout(c);                                           // round one more to collect the results
         close = true;
       }
     }
@@ -311,8 +330,6 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   __shared__ TW* sh_dst[kMaxRanks];
   const int P = c.P;
   const int cpb = p.sym.cpb;
-  const int tile = p.tile_elems;
-  const int tpc = p.tpc;
   const int wid = blockIdx.x - 1;
   const bool vec = p.vec_ok != 0;
   const TIn* src = static_cast<const TIn*>(p.a.src[c.vr]);
@@ -338,6 +355,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
 
   // ---- phase S: scatter my message, chunk-major, destinations rotated from self ----
   {
+    const int tile = p.part_s, tpc = p.tpc_s;
     const int items = cpb * P * tpc;
     for (int item = wid; item < items; item += p.a.ctas) {
       const int k = item % tpc;
@@ -373,6 +391,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     const int nch = num_chunks(bsize, p.a.max_chunk);
     const uint32_t* arr = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_arr) + p.sym.arr_index(c.slot, 0, 0);
     const TW* scat0 = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, 0);
+    const int tile = p.part_r, tpc = p.tpc_r;
     const int items = nch * tpc;
     for (int item = wid; item < items; item += p.a.ctas) {
       const int k = item % tpc;
@@ -442,6 +461,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     const uint32_t* cw = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_complete);
     const uint32_t* bitmap = cw + 4;
     const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + p.sym.arr_index(c.slot, 0, 0);
+    const int tile = p.part_s, tpc = p.tpc_s;
     const int items = cpb * P * tpc;
     for (int item = wid; item < items; item += p.a.ctas) {
       const int k = item % tpc;
@@ -466,7 +486,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
             present = (ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u;
             break;
           }
-          if (globaltimer_ns() > c.deadline + 1000000000ull) {  // the control CTA never answered
+          if (globaltimer_ns() > c.deadline + 2 * p.a.timeout_ns + 1000000000ull) {  // the control CTA never answered
             note_timeout(c);
             break;
           }
@@ -579,10 +599,21 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
   kp.total_chunks = total_reduced_chunks(kp.part, a->max_chunk);
   const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
   const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);
-  kp.tile_elems = kThreads * kUnitsPerThread * unit_elems;
-  kp.tpc = static_cast<int>(ceil_div(a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1),
-                                     kp.tile_elems));
-  if (kp.tpc < 1) kp.tpc = 1;
+  // Work items: a chunk is cut into equal parts (multiples of one full CTA sweep) so that each phase has
+  // about two items per CTA; flags stay per chunk, a self-resetting counter tells the last part to raise it.
+  const int64_t sweep = static_cast<int64_t>(kThreads) * kUnitsPerThread * unit_elems;
+  const int64_t chunk_len = a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1);
+  auto split = [&](int64_t items_without_split, int& part, int& tpc) {
+    int64_t want = ceil_div(2 * static_cast<int64_t>(a->ctas), items_without_split > 0 ? items_without_split : 1);
+    const int64_t most = ceil_div(chunk_len, sweep);
+    if (want > most) want = most;
+    if (want < 1) want = 1;
+    int64_t len = ceil_div(ceil_div(chunk_len, want), sweep) * sweep;
+    part = static_cast<int>(len);
+    tpc = static_cast<int>(ceil_div(chunk_len, len));
+  };
+  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.part_s, kp.tpc_s);
+  split(kp.sym.cpb, kp.part_r, kp.tpc_r);
   // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
   const int64_t align_elems = 16 / (in_bytes < wb ? in_bytes : wb);
   bool vec = (kp.sym.block % align_elems == 0) && (a->max_chunk % align_elems == 0 || a->max_chunk >= kp.sym.block);

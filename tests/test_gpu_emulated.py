@@ -135,13 +135,13 @@ def test_completion_threshold_with_straggling_owner():
     for i in range(3):
         assert torch.equal(outs[i][:lo], part[:lo]) and bool((counts[i][:lo] == 3).all())
         assert bool((outs[i][lo:] == 0).all()) and bool((counts[i][lo:] == 0).all())
-    # the straggler itself: the others' blocks were reduced without it (3); its own block fires on the
-    # first poll that sees >= 3 arrivals, which may or may not include its own contribution yet
+    # the straggler itself: the others' blocks were reduced without it (3 contributors).  Its own block is
+    # timing dependent — its control CTA may close the round at 75% before its delayed CTAs reduce it.
     assert bool((counts[3][:lo] == 3).all()) and torch.equal(outs[3][:lo], part[:lo])
     own = counts[3][lo:]
-    assert bool(((own == 3) | (own == 4)).all())
     full = _ref_sum(srcs)
-    assert torch.equal(torch.where(own == 4, full[lo:], part[lo:]), outs[3][lo:])
+    want_own = torch.where(own == 4, full[lo:], torch.where(own == 3, part[lo:], torch.zeros_like(part[lo:])))
+    assert bool(((own == 0) | (own == 3) | (own == 4)).all()) and torch.equal(outs[3][lo:], want_own)
     assert cl.timeouts_seen() == [0] * world
 
 
