@@ -13,6 +13,7 @@ flags, the geometry — and fills the ``AarLaunch`` struct.  Two front ends use 
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import torch
@@ -58,7 +59,7 @@ class RoundLauncher:
         g = self.geo
         a.world, a.algo = g.world, self.algo
         a.in_dtype, a.wire_dtype = self.in_code, self.wire_code
-        a.ctas, a.use_tma = self.ctas, 0
+        a.ctas, a.use_tma = self.ctas, 0 if os.environ.get("AAR_NO_TMA") else 1
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate

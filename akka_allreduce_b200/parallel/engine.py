@@ -34,7 +34,7 @@ class DeviceAllreduce:
                  th_reduce: float = 1.0, th_complete: float = 1.0, th_allreduce: float | None = None,
                  device: int | None = None, uds_dir: str | None = None, multicast: bool = True,
                  align_blocks: bool = True, ctas: int | None = None, timeout_ms: float = 2000.0,
-                 scale: float = 1.0, normalize: bool = False):
+                 scale: float = 1.0, normalize: bool = False, algo: str = "auto"):
         self.rank, self.world = rank, world
         self.device_index = torch.cuda.current_device() if device is None else device
         self.device = torch.device("cuda", self.device_index)
@@ -45,6 +45,8 @@ class DeviceAllreduce:
         self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
                                       ctas or default_ctas(n * elem), timeout_ms, scale, normalize)
         lib = self.launcher.lib
+        if algo not in ("auto", "twoshot", "nvls"):
+            raise ValueError(f"unknown algo {algo!r}")
         self._heap = C.c_void_p()
         K.check(lib.aar_heap_create(C.byref(self._heap), rank, world, self.device_index, self.launcher.sym_bytes,
                                     (uds_dir or default_uds_dir()).encode(), int(multicast)), "aar_heap_create")
@@ -53,6 +55,13 @@ class DeviceAllreduce:
         K.check(lib.aar_heap_ptrs(self._heap, bases, C.byref(mc)), "aar_heap_ptrs")
         self.peer_ptrs = [int(bases[i]) for i in range(world)]
         self.mc_ptr = mc.value  # None when the driver exposes no multicast
+        # NVLS reduces inside the switch over ALL ranks, so it is only eligible when no contribution may be
+        # left out (thReduce = 1); chunks that time out fall back to unicast pulls inside the same kernel.
+        nvls_ok = bool(self.mc_ptr) and world > 1 and self.launcher.req_reduce >= world
+        if algo == "nvls" and not nvls_ok:
+            raise K.AarError("algo=nvls needs a multicast alias (NVLS), world > 1 and thReduce = 1")
+        self.algo = "nvls" if (algo == "nvls" or (algo == "auto" and nvls_ok and os.environ.get("AAR_NO_NVLS") is None)) else "twoshot"
+        self.launcher.algo = K.ALGO_NAMES[self.algo]
         self.scratch = torch.zeros(self.launcher.scratch_bytes, dtype=torch.uint8, device=self.device)
         self.host_flags = torch.zeros(4, dtype=torch.int32).pin_memory()
         self.round = 0

@@ -127,7 +127,7 @@ def main() -> int:
     busbw = algbw * 2 * (world - 1) / world
 
     extras = {"busbw_GBps": round(busbw, 2), "algbw_per_rank_GBps": round(algbw, 2), "correct": ok,
-              "max_rel_err": err, "multicast": eng.has_multicast, "ctas": eng.launcher.ctas,
+              "max_rel_err": err, "multicast": eng.has_multicast, "algo": eng.algo, "ctas": eng.launcher.ctas,
               "timeouts": eng.timeouts_seen()}
 
     # ------------------------------------------------------------------ NCCL all_reduce, same message

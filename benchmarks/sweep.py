@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--dtype", default="float32")
     ap.add_argument("--out", default="")
     ap.add_argument("--no-nccl", action="store_true")
+    ap.add_argument("--algo", default="auto")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -99,23 +100,25 @@ def main():
                     srcs = [torch.randn(n, device=dev).to(dtype) for _ in range(P)]
                     ms = timed(lambda i: cl.run_round(srcs), args.iters, args.warmup)
                     used = cl.launcher.ctas
+                    algo_used = "twoshot"
                     del cl, srcs
                 else:
                     from akka_allreduce_b200.parallel.engine import DeviceAllreduce, default_uds_dir
 
                     eng = DeviceAllreduce(rank, world, n, mc, max_lag=1, dtype=dtype, th_allreduce=1.0, device=local,
-                                          uds_dir=default_uds_dir(), ctas=ctas or None, timeout_ms=10_000)
+                                          uds_dir=default_uds_dir(), ctas=ctas or None, timeout_ms=10_000, algo=args.algo)
                     srcs = [torch.randn(n, device=dev).to(dtype) for _ in range(nsrc)]
                     outs = [torch.empty(n, dtype=dtype, device=dev) for _ in range(2)]
                     cnts = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(2)]
                     ms = timed(lambda i: eng.allreduce(srcs[i % nsrc], outs[i % 2], cnts[i % 2]), args.iters, args.warmup)
                     used = eng.launcher.ctas
+                    algo_used = eng.algo
                     eng.close()
                     del srcs, outs, cnts
                 alg = n * esz / (ms * 1e-3) / 1e9
                 row = {"bytes": n * esz, "chunk_bytes": mc * esz, "workers": P, "gpus": world, "ctas": used,
                        "ms": round(ms, 5), "algbw_GBps": round(alg, 2), "busbw_GBps": round(alg * 2 * (P - 1) / P, 2),
-                       "emulated": bool(args.emulate), "dtype": args.dtype}
+                       "emulated": bool(args.emulate), "dtype": args.dtype, "algo": algo_used}
                 if nccl_ms is not None:
                     row["nccl_ms"] = round(nccl_ms, 5)
                     row["nccl_busbw_GBps"] = round(n * esz / (nccl_ms * 1e-3) / 1e9 * 2 * (P - 1) / P, 2)

@@ -124,6 +124,35 @@ __device__ __forceinline__ __nv_bfloat16 ld_fresh_scalar(const __nv_bfloat16* p)
   return *reinterpret_cast<__nv_bfloat16*>(&u);
 }
 
+// ---------------------------------------------------------------- NVLS multicast (multimem.*)
+// `p` is an address inside the multicast alias of the symmetric region: a load is answered by the
+// NVSwitch with the element-wise sum over every rank's copy, a store is replicated to every rank.
+template <typename T>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add(const uint4* p);
+template <>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add<float>(const uint4* p) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+template <>
+__device__ __forceinline__ uint4 multimem_ld_reduce_add<__nv_bfloat16>(const uint4* p) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(uint4* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
 // ---------------------------------------------------------------- mbarrier + TMA bulk (1-D)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 

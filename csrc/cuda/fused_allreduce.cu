@@ -103,12 +103,13 @@ __device__ __forceinline__ void push_tile(const TIn* __restrict__ src, TW* __res
   }
 }
 
-// Sum of the arrived peers' rows (local, written by peers) -> every peer's sink row.
+// Sum of the arrived peers' rows -> every peer's sink row.  `rows[s]` is where peer s's contribution
+// to this tile lives: my own scat slot (push mode) or peer s's staging slot over NVLink (pull mode).
 // B units per thread per sweep and 8/B peers per load batch: eight 16-byte loads in flight per thread
 // whatever the peer count; every element is still accumulated in peer order 0..P-1.
 template <typename TW, int B>
-__device__ __forceinline__ void reduce_units(const TW* __restrict__ scat0, int64_t row_stride, uint32_t mask, int P,
-                                             TW* const* __restrict__ dst, int units, float post) {
+__device__ __forceinline__ void reduce_units(const TW* const* __restrict__ rows, uint32_t mask, int P,
+                                             TW* const* __restrict__ dst, int ndst, int units, float post) {
   constexpr int E = 16 / sizeof(TW);
   constexpr int PB = 8 / B;
   using U = Unit<TW, E>;
@@ -126,8 +127,7 @@ __device__ __forceinline__ void reduce_units(const TW* __restrict__ scat0, int64
 #pragma unroll
         for (int j = 0; j < PB; ++j) {
           const int u = u0 + b * kThreads, s = s0 + j;
-          if (u < units && s < P && ((mask >> s) & 1u))
-            r[b][j] = ld_fresh(reinterpret_cast<const raw_t*>(scat0 + s * row_stride) + u);
+          if (u < units && s < P && ((mask >> s) & 1u)) r[b][j] = ld_fresh(reinterpret_cast<const raw_t*>(rows[s]) + u);
         }
 #pragma unroll
       for (int b = 0; b < B; ++b)
@@ -149,30 +149,67 @@ __device__ __forceinline__ void reduce_units(const TW* __restrict__ scat0, int64
 #pragma unroll
         for (int e = 0; e < E; ++e) acc[b][e] *= post;
         const raw_t out = U::pack(acc[b]);
-        for (int q = 0; q < P; ++q) reinterpret_cast<raw_t*>(dst[q])[u] = out;
+        for (int q = 0; q < ndst; ++q) reinterpret_cast<raw_t*>(dst[q])[u] = out;
       }
     }
   }
 }
 
 template <typename TW>
-__device__ __forceinline__ void reduce_tile(const TW* __restrict__ scat0, int64_t row_stride, uint32_t mask, int P,
-                                            TW* const* __restrict__ dst, int len, float post, bool vec) {
+__device__ __forceinline__ void reduce_tile(const TW* const* __restrict__ rows, uint32_t mask, int P,
+                                            TW* const* __restrict__ dst, int ndst, int len, float post, bool vec) {
   constexpr int E = 16 / sizeof(TW);
   int done = 0;
   if (vec) {
     const int units = len / E;
-    if (P <= 2) reduce_units<TW, 4>(scat0, row_stride, mask, P, dst, units, post);
-    else if (P <= 4) reduce_units<TW, 2>(scat0, row_stride, mask, P, dst, units, post);
-    else reduce_units<TW, 1>(scat0, row_stride, mask, P, dst, units, post);
+    constexpr int BMAX = E == 8 ? 2 : 4;  // 8-wide units carry twice the accumulators
+    if (P <= 2) reduce_units<TW, BMAX>(rows, mask, P, dst, ndst, units, post);
+    else if (P <= 4) reduce_units<TW, 2>(rows, mask, P, dst, ndst, units, post);
+    else reduce_units<TW, 1>(rows, mask, P, dst, ndst, units, post);
     done = units * E;
   }
   for (int i = done + threadIdx.x; i < len; i += kThreads) {
     float acc = 0.f;
     for (int s = 0; s < P; ++s)
-      if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(scat0 + s * row_stride + i));
+      if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(rows[s] + i));
     const TW o = from_float<TW>(acc * post);
-    for (int q = 0; q < P; ++q) dst[q][i] = o;
+    for (int q = 0; q < ndst; ++q) dst[q][i] = o;
+  }
+}
+
+// NVLS form of the same tile: one multimem.ld_reduce pulls the switch-reduced sum of every rank's
+// staging slot, one multimem.st lands the result in every rank's sink slot.  Only used when all P
+// contributions are present (an in-switch reduction cannot leave a peer out).
+template <typename TW>
+__device__ __forceinline__ void nvls_reduce_tile(const TW* __restrict__ mc_src, TW* __restrict__ mc_dst, int len,
+                                                 float post) {
+  constexpr int E = 16 / sizeof(TW);
+  constexpr int B = 8;
+  using U = Unit<TW, E>;
+  const int units = len / E;
+  const uint4* s = reinterpret_cast<const uint4*>(mc_src);
+  uint4* d = reinterpret_cast<uint4*>(mc_dst);
+  for (int u0 = threadIdx.x; u0 < units; u0 += kThreads * B) {
+    uint4 r[B];
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      const int u = u0 + j * kThreads;
+      if (u < units) r[j] = multimem_ld_reduce_add<TW>(s + u);
+    }
+#pragma unroll
+    for (int j = 0; j < B; ++j) {
+      const int u = u0 + j * kThreads;
+      if (u < units) {
+        if (post != 1.f) {
+          float v[E];
+          U::unpack(r[j], v);
+#pragma unroll
+          for (int e = 0; e < E; ++e) v[e] *= post;
+          r[j] = U::pack(v);
+        }
+        multimem_st(d + u, r[j]);
+      }
+    }
   }
 }
 
@@ -322,24 +359,101 @@ __device__ void control_cta(const KParams& p, const Ctx& c) {
   }
 }
 
+// ---------------------------------------------------------------- TMA staging ring
+// Pure copies (scatter of an unconverted source, flush of the sink slot) never touch registers:
+// one elected thread streams 32 KB tiles global -> shared -> global with cp.async.bulk, three
+// loads ahead of the store.  The destination may be a peer GPU (the store goes out over NVLink).
+constexpr int kStageBytes = 32768;
+constexpr int kStages = 4;
+constexpr int kSmemBytes = (kStages + 1) * kStageBytes + 64;  // ring + one tile of counts + mbarriers
+
+struct TmaRing {
+  uint8_t* buf;
+  uint8_t* cnt_tile;
+  uint64_t* full;
+  uint32_t issued;  // tiles this CTA has pushed through the ring so far (stage and parity bookkeeping)
+};
+
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+  const uint64_t t0 = globaltimer_ns();
+  while (!mbar_try_wait(bar, parity))
+    if (globaltimer_ns() - t0 > 4000000000ull) __trap();  // a bulk copy that never lands is a bug, not a wait
+}
+
+// Thread 0 only.  `bytes` and both pointers are 16-byte aligned.  With `counts_dst`, every data tile is
+// followed by the matching stretch of the pre-filled counts tile (elem_bytes = size of a data element).
+__device__ __forceinline__ void tma_copy(TmaRing& R, uint8_t* dst, const uint8_t* src, int64_t bytes,
+                                         uint8_t* counts_dst, int elem_bytes) {
+  const int nt = static_cast<int>((bytes + kStageBytes - 1) / kStageBytes);
+  const uint32_t base = R.issued;
+  auto tile_bytes = [&](int i) -> uint32_t {
+    const int64_t left = bytes - static_cast<int64_t>(i) * kStageBytes;
+    return static_cast<uint32_t>(left < kStageBytes ? left : kStageBytes);
+  };
+  auto issue_load = [&](int i) {
+    const uint32_t st = (base + i) % kStages;
+    mbar_expect_tx(&R.full[st], tile_bytes(i));
+    tma_load_1d(R.buf + st * kStageBytes, src + static_cast<int64_t>(i) * kStageBytes, tile_bytes(i), &R.full[st]);
+  };
+  for (int i = 0; i < nt && i < kStages - 1; ++i) issue_load(i);
+  for (int i = 0; i < nt; ++i) {
+    const uint32_t st = (base + i) % kStages;
+    mbar_wait_bounded(&R.full[st], ((base + i) / kStages) & 1u);
+    const uint32_t tb = tile_bytes(i);
+    tma_store_1d(dst + static_cast<int64_t>(i) * kStageBytes, R.buf + st * kStageBytes, tb);
+    if (counts_dst != nullptr) {
+      uint32_t cb = tb / elem_bytes * 4;  // bytes of int32 counts covering this tile
+      uint8_t* cd = counts_dst + static_cast<int64_t>(i) * (kStageBytes / elem_bytes) * 4;
+      while (cb > 0) {
+        const uint32_t piece = cb < static_cast<uint32_t>(kStageBytes) ? cb : kStageBytes;
+        tma_store_1d(cd, R.cnt_tile, piece);
+        cd += piece;
+        cb -= piece;
+      }
+    }
+    tma_commit();
+    if (i + kStages - 1 < nt) {
+      tma_wait_read<1>();  // every store but the newest has finished reading its stage
+      issue_load(i + kStages - 1);
+    }
+  }
+  tma_wait_all<0>();  // all stores complete before any flag is raised or the ring is reused
+  asm volatile("fence.proxy.async;" ::: "memory");
+  R.issued = base + nt;
+}
+
 // ---------------------------------------------------------------- work CTAs
-template <typename TIn, typename TW>
+template <typename TIn, typename TW, bool kNvls>
 __device__ void work_cta(const KParams& p, const Ctx& c) {
+  extern __shared__ __align__(1024) uint8_t dyn_smem[];
   __shared__ uint32_t sh_word;
   __shared__ int sh_cnt;
+  __shared__ int sh_tile_cnt;
   __shared__ TW* sh_dst[kMaxRanks];
+  __shared__ const TW* sh_rows[kMaxRanks];
   const int P = c.P;
   const int cpb = p.sym.cpb;
   const int wid = blockIdx.x - 1;
   const bool vec = p.vec_ok != 0;
+  const bool tma = vec && p.a.use_tma != 0;
   const TIn* src = static_cast<const TIn*>(p.a.src[c.vr]);
   TIn* out = static_cast<TIn*>(p.a.out[c.vr]);
   int32_t* counts = p.a.counts[c.vr];
   uint32_t* scat_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt);
   uint32_t* red_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt);
   uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask);
+  TmaRing ring;
+  ring.buf = dyn_smem;
+  ring.cnt_tile = dyn_smem + kStages * kStageBytes;
+  ring.full = reinterpret_cast<uint64_t*>(dyn_smem + (kStages + 1) * kStageBytes);
+  ring.issued = 0;
 
   if (threadIdx.x == 0) {
+    if (tma) {
+      for (int i = 0; i < kStages; ++i) mbar_init(&ring.full[i], 1);
+      fence_barrier_init();
+    }
+    sh_tile_cnt = -1;
     if (p.a.delay_ns[c.rank] != 0) {  // injected straggler
       const uint64_t until = globaltimer_ns() + p.a.delay_ns[c.rank];
       while (globaltimer_ns() < until) __nanosleep(256);
@@ -349,12 +463,16 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   }
   __syncthreads();
   const uint32_t dest_ok = sh_word;
+  const uint32_t all_ranks = P >= 32 ? 0xffffffffu : ((1u << P) - 1u);
   const bool muted = (p.a.mute_mask >> c.rank) & 1u;
   const uint32_t skip = p.a.skip_dest_mask[c.rank];
   __syncthreads();
 
   // ---- phase S: scatter my message, chunk-major, destinations rotated from self ----
+  // Push mode: the slice for owner d goes straight into d's scat row [me] over NVLink.
+  // NVLS mode: it is staged in MY scat row [d]; the switch will pull and sum it.
   {
+    const bool pure_copy = tma && sizeof(TIn) == sizeof(TW) && p.a.scale == 1.0f;
     const int tile = p.part_s, tpc = p.tpc_s;
     const int items = cpb * P * tpc;
     for (int item = wid; item < items; item += p.a.ctas) {
@@ -369,13 +487,21 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       if (muted || ((skip >> d) & 1u) || !((dest_ok >> d) & 1u)) continue;
       const int64_t off = cb + static_cast<int64_t>(k) * tile;
       const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
-      TW* dst = reinterpret_cast<TW*>(p.a.sym[d] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off;
-      push_tile<TIn, TW>(src + p.part.start(d) + off, dst, len, p.a.scale, vec);
+      TW* dst = kNvls ? reinterpret_cast<TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, d) + off
+                      : reinterpret_cast<TW*>(p.a.sym[d] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off;
+      const TIn* from = src + p.part.start(d) + off;
+      if (pure_copy && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
+        if (threadIdx.x == 0)
+          tma_copy(ring, reinterpret_cast<uint8_t*>(dst), reinterpret_cast<const uint8_t*>(from),
+                   static_cast<int64_t>(len) * sizeof(TW), nullptr, sizeof(TW));
+      } else {
+        push_tile<TIn, TW>(from, dst, len, p.a.scale, vec);
+      }
       __syncthreads();
       if (threadIdx.x == 0) {
         __threadfence_system();
         uint32_t* cnt = scat_cnt + d * cpb + ch;
-        if (atomicAdd(cnt, 1u) == static_cast<uint32_t>(ntiles - 1)) {  // chunk fully pushed: ScatterBlock sent
+        if (atomicAdd(cnt, 1u) == static_cast<uint32_t>(ntiles - 1)) {  // chunk fully out: ScatterBlock sent
           st_volatile(cnt, 0u);
           __threadfence_system();
           st_release_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch),
@@ -390,7 +516,6 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     const int64_t bsize = p.part.size(c.rank);
     const int nch = num_chunks(bsize, p.a.max_chunk);
     const uint32_t* arr = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_arr) + p.sym.arr_index(c.slot, 0, 0);
-    const TW* scat0 = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, 0);
     const int tile = p.part_r, tpc = p.tpc_r;
     const int items = nch * tpc;
     for (int item = wid; item < items; item += p.a.ctas) {
@@ -427,17 +552,27 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       }
       if (threadIdx.x < P) {
         const int q = (threadIdx.x + c.rank) % P;
-        TW* base = reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off;
+        TW* mine = reinterpret_cast<TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off;
         // A peer that is skipped this launch gets its copy redirected to my own sink row.
         sh_dst[threadIdx.x] = ((dest_ok >> q) & 1u)
-                                  ? base
-                                  : reinterpret_cast<TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off;
+                                  ? reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off
+                                  : mine;
+        const int s = threadIdx.x;
+        sh_rows[s] = kNvls ? reinterpret_cast<const TW*>(p.a.sym[s] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off
+                           : reinterpret_cast<const TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, s) + off;
       }
       __syncthreads();
       const uint32_t mask = sh_word;
       const int cnt = __popc(mask);
       const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
-      reduce_tile<TW>(scat0 + off, p.sym.block_pad, mask, P, sh_dst, len, post, vec);
+      constexpr int EW = 16 / sizeof(TW);
+      if (kNvls && mask == all_ranks && dest_ok == all_ranks && vec && len % EW == 0) {
+        const int64_t so = p.sym.off_scat + (p.sym.scat_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
+        const int64_t to = p.sym.off_sink + (p.sym.sink_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
+        nvls_reduce_tile<TW>(reinterpret_cast<const TW*>(p.a.mc_base + so), reinterpret_cast<TW*>(p.a.mc_base + to), len, post);
+      } else {
+        reduce_tile<TW>(sh_rows, mask, P, sh_dst, P, len, post, vec);
+      }
       __syncthreads();
       if (threadIdx.x == 0) {
         __threadfence_system();
@@ -461,6 +596,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     const uint32_t* cw = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_complete);
     const uint32_t* bitmap = cw + 4;
     const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + p.sym.arr_index(c.slot, 0, 0);
+    const bool pure_copy = tma && sizeof(TIn) == sizeof(TW);
     const int tile = p.part_s, tpc = p.tpc_s;
     const int items = cpb * P * tpc;
     for (int item = wid; item < items; item += p.a.ctas) {
@@ -502,7 +638,21 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       const int cnt = sh_cnt;
       const TW* sink = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, o) + off;
       const int64_t g = p.part.start(o) + off;
-      flush_tile<TW, TIn>(sink, out + g, counts != nullptr ? counts + g : nullptr, len, present, cnt, vec);
+      if (pure_copy && present && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
+        if (counts != nullptr && sh_tile_cnt != cnt) {  // (re)fill the shared tile of counts
+          int4* ct = reinterpret_cast<int4*>(ring.cnt_tile);
+          for (int i = threadIdx.x; i < kStageBytes / 16; i += kThreads) ct[i] = make_int4(cnt, cnt, cnt, cnt);
+          fence_proxy_async_smem();
+          __syncthreads();
+          if (threadIdx.x == 0) sh_tile_cnt = cnt;
+        }
+        if (threadIdx.x == 0)
+          tma_copy(ring, reinterpret_cast<uint8_t*>(out + g), reinterpret_cast<const uint8_t*>(sink),
+                   static_cast<int64_t>(len) * sizeof(TW), counts != nullptr ? reinterpret_cast<uint8_t*>(counts + g) : nullptr,
+                   sizeof(TW));
+      } else {
+        flush_tile<TW, TIn>(sink, out + g, counts != nullptr ? counts + g : nullptr, len, present, cnt, vec);
+      }
       __syncthreads();
     }
   }
@@ -510,7 +660,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   if (threadIdx.x == 0) finish_cta(p, c);
 }
 
-template <typename TIn, typename TW>
+template <typename TIn, typename TW, bool kNvls>
 __global__ void __launch_bounds__(kThreads, 1) aar_twoshot_kernel(const __grid_constant__ KParams p) {
   Ctx c;
   c.vr = p.a.emu ? blockIdx.y : 0;
@@ -523,7 +673,7 @@ __global__ void __launch_bounds__(kThreads, 1) aar_twoshot_kernel(const __grid_c
   c.host = p.a.host_flags != nullptr ? p.a.host_flags + 4 * c.vr : nullptr;
   c.deadline = globaltimer_ns() + p.a.timeout_ns;
   if (blockIdx.x == 0) control_cta(p, c);
-  else work_cta<TIn, TW>(p, c);
+  else work_cta<TIn, TW, kNvls>(p, c);
 }
 
 // ---------------------------------------------------------------- host side
@@ -533,20 +683,33 @@ int fail(int code, const std::string& what) {
   return code;
 }
 
-template <typename TIn, typename TW>
+template <typename TIn, typename TW, bool kNvls>
 int launch_twoshot(const KParams& kp, cudaStream_t stream) {
+  auto* fn = aar_twoshot_kernel<TIn, TW, kNvls>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t ea = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
+    if (ea != cudaSuccess) return fail(AAR_ECUDA, std::string("cudaFuncSetAttribute(smem): ") + cudaGetErrorString(ea));
+    configured = true;
+  }
+  const int smem = kp.a.use_tma ? kSmemBytes : 0;
   dim3 grid(kp.a.ctas + 1, kp.a.emu ? kp.a.world : 1);
   cudaError_t e;
   if (kp.a.emu) {
     void* args[] = {const_cast<KParams*>(&kp)};
-    e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(aar_twoshot_kernel<TIn, TW>), grid, dim3(kThreads), args, 0,
-                                    stream);
+    e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(fn), grid, dim3(kThreads), args, smem, stream);
   } else {
-    aar_twoshot_kernel<TIn, TW><<<grid, kThreads, 0, stream>>>(kp);
+    fn<<<grid, kThreads, smem, stream>>>(kp);
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("two-shot launch: ") + cudaGetErrorString(e));
   return 1;
+}
+
+template <typename TIn, typename TW>
+int launch_algo(const KParams& kp, cudaStream_t stream) {
+  if (kp.a.algo == AAR_ALGO_NVLS) return launch_twoshot<TIn, TW, true>(kp, stream);
+  return launch_twoshot<TIn, TW, false>(kp, stream);
 }
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -576,8 +739,9 @@ int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block
 
 int aar_max_emu_ctas(int world, int device) {
   int sms = 0, per_sm = 0;
+  cudaFuncSetAttribute(aar_twoshot_kernel<float, float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
   if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return AAR_ECUDA;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, aar_twoshot_kernel<float, float>, kThreads, 0) != cudaSuccess)
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, aar_twoshot_kernel<float, float, false>, kThreads, kSmemBytes) != cudaSuccess)
     return AAR_ECUDA;
   const int resident = sms * (per_sm > 0 ? per_sm : 1);
   return resident / world - 1;
@@ -627,10 +791,15 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
     if (a->sym[r] == nullptr) return fail(AAR_EINVAL, "symmetric base pointer missing");
   kp.vec_ok = vec ? 1 : 0;
 
-  if (a->algo != AAR_ALGO_TWOSHOT) return fail(AAR_EUNSUPPORTED, "algorithm not built into this library yet");
-  if (a->in_dtype == AAR_F32 && a->wire_dtype == AAR_F32) return launch_twoshot<float, float>(kp, stream);
-  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_twoshot<__nv_bfloat16, __nv_bfloat16>(kp, stream);
-  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_F32) return launch_twoshot<__nv_bfloat16, float>(kp, stream);
+  if (a->algo == AAR_ALGO_NVLS) {
+    if (a->mc_base == nullptr || a->emu) return fail(AAR_EUNSUPPORTED, "NVLS needs a multicast alias of the symmetric region");
+    if (a->req_reduce < a->world) return fail(AAR_EINVAL, "NVLS reduces in the switch over all ranks: thReduce must be 1");
+  } else if (a->algo != AAR_ALGO_TWOSHOT) {
+    return fail(AAR_EUNSUPPORTED, "algorithm not built into this library yet");
+  }
+  if (a->in_dtype == AAR_F32 && a->wire_dtype == AAR_F32) return launch_algo<float, float>(kp, stream);
+  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_algo<__nv_bfloat16, __nv_bfloat16>(kp, stream);
+  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_F32) return launch_algo<__nv_bfloat16, float>(kp, stream);
   return fail(AAR_EUNSUPPORTED, "dtype combination not supported (f32/f32, bf16/bf16, bf16/f32)");
 }
 
