@@ -38,6 +38,7 @@ HOST_SOURCES = [
 CUDA_SOURCES = [
     "cuda/fused_allreduce.cu",
     "cuda/sym_heap.cu",
+    "cuda/probe.cu",
 ]
 CUDA_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 

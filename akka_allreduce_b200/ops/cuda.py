@@ -40,6 +40,7 @@ class AarLaunch(C.Structure):
         ("mc_base", C.c_void_p),
         ("scratch", C.c_void_p * MAX_RANKS),
         ("host_flags", C.c_void_p),
+        ("trace", C.c_void_p),
     ]
 
 
@@ -64,6 +65,8 @@ def lib() -> C.CDLL:
     l.aar_sym_flag_bytes.argtypes = [i64, i64, i32, i32, i32, i64, i64]
     l.aar_scratch_bytes.restype = i64
     l.aar_scratch_bytes.argtypes = [i64, i64, i32, i64]
+    l.aar_scratch_force_offset.restype = i64
+    l.aar_scratch_force_offset.argtypes = [i64, i64, i32, i64]
     l.aar_allreduce_round.restype = i32
     l.aar_allreduce_round.argtypes = [C.POINTER(AarLaunch), vp]
     l.aar_max_emu_ctas.restype = i32

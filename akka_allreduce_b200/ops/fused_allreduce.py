@@ -52,6 +52,7 @@ class RoundLauncher:
         self.flag_bytes = self.lib.aar_sym_flag_bytes(geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code,
                                                       os_cap, geo.block_step_arg)
         self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
+        self.force_offset = self.lib.aar_scratch_force_offset(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.launches = 0
 
     def prepare(self, a: K.AarLaunch) -> None:
@@ -146,9 +147,9 @@ class EmulatedCluster:
             a.src[i] = srcs[i].data_ptr()
             a.out[i] = outs[i].data_ptr()
             a.counts[i] = counts[i].data_ptr()
-        if force or self._forced:
-            for i in range(self.world):
-                self.host_flags[4 * i] = (r + 1) if force else 0
+        if force or self._forced:  # the force tag is a device word inside each rank's scratch
+            off = self.launcher.force_offset
+            self.scratch[:, off:off + 4].view(torch.int32).fill_((r + 1) if force else 0)
             self._forced = force
         self.launcher.launch(a)
         if round_ is None:

@@ -64,6 +64,10 @@ class DeviceAllreduce:
         self.launcher.algo = K.ALGO_NAMES[self.algo]
         self.scratch = torch.zeros(self.launcher.scratch_bytes, dtype=torch.uint8, device=self.device)
         self.host_flags = torch.zeros(4, dtype=torch.int32).pin_memory()
+        off = self.launcher.force_offset
+        self._force_word = self.scratch[off:off + 4].view(torch.int32)      # device word the kernels poll
+        self._force_src = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._ctl_stream = torch.cuda.Stream(device=self.device)
         self.round = 0
         self._launch = a = K.AarLaunch()
         self.launcher.prepare(a)
@@ -98,9 +102,35 @@ class DeviceAllreduce:
         if round_ is None:
             self.round += 1
 
+    def enable_trace(self) -> torch.Tensor:
+        """Per-CTA phase timestamps of the LAST launch: int64 [ctas+1, 8] of globaltimer ns
+        (start, gate passed, S done, R done, C done, ns waiting in R, ns waiting in C, 0)."""
+        self.trace = torch.zeros(self.launcher.ctas + 1, 16, dtype=torch.int64, device=self.device)
+        self._launch.trace = self.trace.data_ptr()
+        return self.trace
+
+    def trace_summary(self) -> dict:
+        torch.cuda.synchronize(self.device)
+        t = self.trace[1:].cpu().double()  # work CTAs only (row 0 is the control CTA)
+        t0 = float(t[:, 0].min())
+        us = lambda x: round(float(x) / 1e3, 1)
+        return {"gate_us": us((t[:, 1] - t0).max()), "S_done_us": [us((t[:, 2] - t0).min()), us((t[:, 2] - t0).max())],
+                "R_done_us": [us((t[:, 3] - t0).min()), us((t[:, 3] - t0).max())],
+                "C_done_us": [us((t[:, 4] - t0).min()), us((t[:, 4] - t0).max())],
+                "wait_in_R_us": [us(t[:, 5].min()), us(t[:, 5].max())], "wait_in_C_us": [us(t[:, 6].min()), us(t[:, 6].max())],
+                "publish_in_S_us": [us(t[:, 7].min()), us(t[:, 7].max())],
+                "S_done_sorted_us": [us(x) for x in sorted((t[:, 2] - t0).tolist())[:: max(1, len(t) // 12)]]}
+
     def force_complete(self, round_: int) -> None:
-        """Host side of the catch-up path: any wait of rounds <= ``round_`` closes immediately."""
-        self.host_flags[0] = round_ + 1
+        """Host side of the catch-up path: any wait of rounds <= ``round_`` closes immediately.  The tag
+        travels to the device as a 4-byte async copy on a side stream, so it also reaches kernels that
+        are already running."""
+        if int(self._force_src[0]) >= round_ + 1:
+            return
+        self._ctl_stream.synchronize()
+        self._force_src[0] = round_ + 1
+        with torch.cuda.stream(self._ctl_stream):
+            self._force_word.copy_(self._force_src, non_blocking=True)
 
     def last_done_round(self) -> int:
         return int(self.host_flags[1]) - 1

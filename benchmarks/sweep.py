@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--algo", default="auto")
+    ap.add_argument("--trace", action="store_true", help="print per-phase device timestamps of one extra round")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -113,6 +114,12 @@ def main():
                     ms = timed(lambda i: eng.allreduce(srcs[i % nsrc], outs[i % 2], cnts[i % 2]), args.iters, args.warmup)
                     used = eng.launcher.ctas
                     algo_used = eng.algo
+                    if args.trace:
+                        eng.enable_trace()
+                        if world > 1:
+                            dist.barrier()
+                        eng.allreduce(srcs[0], outs[0], cnts[0])
+                        print(f"[rank {rank}] trace bytes={n * esz} algo={algo_used}: {json.dumps(eng.trace_summary())}", flush=True)
                     eng.close()
                     del srcs, outs, cnts
                 alg = n * esz / (ms * 1e-3) / 1e9

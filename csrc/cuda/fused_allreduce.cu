@@ -58,12 +58,27 @@ struct Ctx {
   uint8_t* my_sym;
   uint8_t* scratch;
   volatile uint32_t* host;
+  const uint32_t* force;  // device word: rounds <= force-1 close their waits immediately (catch-up)
   uint64_t deadline;
 };
 
-__device__ __forceinline__ bool forced(const Ctx& c) { return c.host != nullptr && c.host[0] >= c.tag; }
 __device__ __forceinline__ void note_timeout(const Ctx& c) {
   if (c.host != nullptr) c.host[2] = c.tag;  // last round closed by a timeout (plain store: host memory)
+}
+// The force word lives in DEVICE memory (the host updates it with an async copy): a kernel that polls
+// host memory over PCIe while it waits slows every system-scope fence on the GPU down by an order of
+// magnitude (measured: profiles/fence_probe.md).  Waiting loops still look at it, and at the timer,
+// only every kSlowPoll-th iteration.
+__device__ __forceinline__ bool forced(const Ctx& c) { return ld_volatile(c.force) >= c.tag; }
+constexpr int kSlowPoll = 16;
+__device__ __forceinline__ bool give_up(const Ctx& c, int& spins, uint64_t deadline) {
+  if ((++spins & (kSlowPoll - 1)) != 0) return false;
+  if (forced(c)) return true;
+  if (globaltimer_ns() > deadline) {
+    note_timeout(c);
+    return true;
+  }
+  return false;
 }
 
 // ---------------------------------------------------------------- tile movers
@@ -285,16 +300,15 @@ __device__ __forceinline__ uint32_t decide_dest_mask(const KParams& p, const Ctx
 __device__ __forceinline__ void wait_gate(const KParams& p, const Ctx& c) {
   if (p.a.gate_count <= 0 || c.tag <= 1) return;
   const uint32_t* done = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_done);
+  int spins = 0;
   for (;;) {
     int have = 0;
-    for (int q = 0; q < c.P; ++q) have += (q == c.rank || ld_acquire_sys(done + q) + 1 >= c.tag) ? 1 : 0;
-    if (have >= p.a.gate_count || forced(c)) return;
-    if (globaltimer_ns() > c.deadline) {
-      note_timeout(c);
-      return;
-    }
+    for (int q = 0; q < c.P; ++q) have += (q == c.rank || ld_volatile(done + q) + 1 >= c.tag) ? 1 : 0;
+    if (have >= p.a.gate_count) break;
+    if (give_up(c, spins, c.deadline)) return;
     __nanosleep(64);
   }
+  __threadfence_system();  // acquire side of the peers' CompleteAllreduce
 }
 
 // All CTAs of a rank report here; the last one resets the scratch and publishes completion.
@@ -302,23 +316,91 @@ __device__ __forceinline__ void finish_cta(const KParams& p, const Ctx& c) {
   uint32_t* fin = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_fin_cnt);
   __threadfence();
   const uint32_t old = atomicAdd(fin, 1u);
-  if (old != static_cast<uint32_t>(p.a.ctas)) return;  // ctas work CTAs + the control CTA
+  if (old != static_cast<uint32_t>(p.a.ctas) + 1u) return;  // ctas work CTAs + the two control warps
   st_volatile(fin, 0u);
   st_volatile(fin + 1, 0u);
+  st_volatile(fin + 3, 0u);  // (fin[2] is the host's force tag: not ours to reset)
   uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
   const int words = (c.P * p.sym.cpb + 31) / 32;
   for (int i = 0; i < 4 + words; ++i) st_volatile(cw + i, 0u);
   __threadfence_system();
   for (int i = 0; i < c.P; ++i) {  // CompleteAllreduce(rank, round) to everyone (AllreduceWorker.scala:276)
     const int q = (i + c.rank) % c.P;
-    st_release_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + c.rank, c.tag);
+    st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + c.rank, c.tag);
   }
   if (c.host != nullptr) c.host[1] = c.tag;
 }
 
 // ---------------------------------------------------------------- control CTA
+// Publisher warp: the only place flags leave this rank.  Data CTAs just bump a local counter per
+// (destination, chunk) behind a gpu-scope fence; this warp polls the counters, and whenever some chunks
+// have all their parts in it pays ONE system-scope fence for the whole batch and then raises their flags
+// on the peers.  (A system-scope fence waits for the NVLink traffic of the whole GPU to drain — tens of
+// microseconds under load, see profiles/fence_probe.md — so data CTAs must never sit in one.)
+__device__ void publisher_warp(const KParams& p, const Ctx& c) {
+  const int lane = threadIdx.x & 31;
+  const int P = c.P, cpb = p.sym.cpb;
+  uint32_t* scat_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt);
+  uint32_t* red_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt);
+  uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask);
+  const uint32_t* fin = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_fin_cnt);
+  const int s_entries = P * cpb;
+  const int entries = s_entries + cpb;
+  const int64_t my_bsize = p.part.size(c.rank);
+  bool last_pass = false;
+  for (;;) {
+    const bool closing = ld_volatile(fin + 3) >= static_cast<uint32_t>(p.a.ctas);  // read BEFORE the scan
+    for (int base = 0; base < entries; base += 32) {
+      const int e = base + lane;
+      bool ready = false;
+      int d = 0, ch = 0;
+      if (e < s_entries) {  // ScatterBlock (d, ch): all parts pushed?
+        d = e / cpb;
+        ch = e % cpb;
+        const int64_t bs = p.part.size(d);
+        if (ch < num_chunks(bs, p.a.max_chunk)) {
+          const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s));
+          ready = ld_volatile(scat_cnt + e) == static_cast<uint32_t>(want);
+        }
+      } else if (e < entries) {  // ReduceBlock (me, ch): all parts reduced and broadcast?
+        ch = e - s_entries;
+        if (ch < num_chunks(my_bsize, p.a.max_chunk)) {
+          const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, my_bsize) - chunk_begin(ch, p.a.max_chunk, my_bsize), p.part_r));
+          ready = ld_volatile(red_cnt + ch) == static_cast<uint32_t>(want);
+        }
+      }
+      if (__any_sync(0xffffffffu, ready)) {
+        __threadfence_system();  // one fence for every chunk of this batch
+        if (ready && e < s_entries) {
+          st_volatile(scat_cnt + e, 0u);
+          st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
+        } else if (ready) {
+          const uint32_t mask = ld_volatile(red_mask + ch) & ~kDecided;
+          const uint32_t dest_ok = ld_volatile(fin + 1) & ~kDecided;
+          st_volatile(red_cnt + ch, 0u);
+          st_volatile(red_mask + ch, 0u);
+          const uint64_t f = (static_cast<uint64_t>(c.tag) << 32) | static_cast<uint32_t>(__popc(mask));
+          for (int i = 0; i < P; ++i) {
+            const int q = (i + c.rank) % P;
+            if ((dest_ok >> q) & 1u)
+              st_relaxed_sys(reinterpret_cast<uint64_t*>(p.a.sym[q] + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
+          }
+        }
+      }
+    }
+    if (last_pass) break;
+    if (closing) last_pass = true;  // every work CTA is past phase R: one more scan picks up the rest
+    else __nanosleep(40);
+  }
+  if (lane == 0) finish_cta(p, c);
+}
+
 __device__ void control_cta(const KParams& p, const Ctx& c) {
-  if (threadIdx.x >= 32) return;
+  if (threadIdx.x >= 64) return;
+  if (threadIdx.x >= 32) {
+    publisher_warp(p, c);
+    return;
+  }
   const int lane = threadIdx.x;
   const int cpb = p.sym.cpb;
   const int entries = c.P * cpb;
@@ -326,6 +408,7 @@ __device__ void control_cta(const KParams& p, const Ctx& c) {
   const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + (int64_t)c.slot * entries;
   uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
   uint32_t* bitmap = cw + 4;
+  int spins = 0;
   for (;;) {
     int seen = 0;
     for (int w = 0; w < words; ++w) {
@@ -334,23 +417,17 @@ __device__ void control_cta(const KParams& p, const Ctx& c) {
       if (idx < entries) {
         const int o = idx / cpb, ch = idx % cpb;
         if (ch < num_chunks(p.part.size(o), p.a.max_chunk))
-          present = static_cast<uint32_t>(ld_acquire_sys(rflag + idx) >> 32) == c.tag;
+          present = static_cast<uint32_t>(ld_volatile64(rflag + idx) >> 32) == c.tag;
       }
       const uint32_t m = __ballot_sync(0xffffffffu, present);
       seen += __popc(m);
-      if (lane == 0) st_volatile(bitmap + w, m);
+      if (lane == 0 && m != 0) st_volatile(bitmap + w, m);
     }
     bool close = seen >= p.a.req_complete || seen >= p.total_chunks;
-    if (!close && lane == 0) {
-      if (forced(c)) close = true;
-      else if (globaltimer_ns() > c.deadline + p.a.timeout_ns) {  // owners get one timeout to reduce, the
-        note_timeout(c);                                           // round one more to collect the results
-        close = true;
-      }
-    }
-    close = __shfl_sync(0xffffffffu, close ? 1 : 0, 0) != 0 || close;
+    if (!close && lane == 0) close = give_up(c, spins, c.deadline + p.a.timeout_ns);  // owners get one timeout to
+    close = __shfl_sync(0xffffffffu, close ? 1 : 0, 0) != 0 || close;                 // reduce, the round one more
     if (close) break;
-    __nanosleep(100);
+    __nanosleep(200);
   }
   if (lane == 0) {
     __threadfence();
@@ -442,6 +519,11 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   uint32_t* scat_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt);
   uint32_t* red_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt);
   uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask);
+  uint64_t* trace = p.a.trace != nullptr
+                        ? p.a.trace + (static_cast<int64_t>(c.vr) * (p.a.ctas + 1) + blockIdx.x) * 16
+                        : nullptr;
+  uint64_t wait_r = 0, wait_c = 0, pub_s = 0;
+  if (trace != nullptr && threadIdx.x == 0) trace[0] = globaltimer_ns();
   TmaRing ring;
   ring.buf = dyn_smem;
   ring.cnt_tile = dyn_smem + kStages * kStageBytes;
@@ -460,6 +542,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     }
     wait_gate(p, c);
     sh_word = decide_dest_mask(p, c);
+    if (trace != nullptr) trace[1] = globaltimer_ns();
   }
   __syncthreads();
   const uint32_t dest_ok = sh_word;
@@ -498,18 +581,15 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
         push_tile<TIn, TW>(from, dst, len, p.a.scale, vec);
       }
       __syncthreads();
-      if (threadIdx.x == 0) {
-        __threadfence_system();
-        uint32_t* cnt = scat_cnt + d * cpb + ch;
-        if (atomicAdd(cnt, 1u) == static_cast<uint32_t>(ntiles - 1)) {  // chunk fully out: ScatterBlock sent
-          st_volatile(cnt, 0u);
-          __threadfence_system();
-          st_release_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch),
-                         c.tag);
-        }
+      if (threadIdx.x == 0) {  // the publisher warp of the control CTA raises the flag once all parts are in
+        const uint64_t w0 = trace != nullptr ? globaltimer_ns() : 0;
+        __threadfence();
+        atomicAdd(scat_cnt + d * cpb + ch, 1u);
+        if (trace != nullptr) pub_s += globaltimer_ns() - w0;
       }
     }
   }
+  if (trace != nullptr && threadIdx.x == 0) trace[2] = globaltimer_ns();
 
   // ---- phase R: reduce my block chunk by chunk and broadcast ----
   {
@@ -527,28 +607,27 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       const int64_t off = cb + static_cast<int64_t>(k) * tile;
       const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
       if (threadIdx.x == 0) {
+        const uint64_t w0 = trace != nullptr ? globaltimer_ns() : 0;
         uint32_t m = ld_volatile(red_mask + ch);
+        int spins = 0;
         while (!(m & kDecided)) {
           uint32_t have = 0;
           for (int s = 0; s < P; ++s)
-            if (ld_acquire_sys(arr + s * cpb + ch) == c.tag) have |= 1u << s;
-          bool fire = __popc(have) >= p.a.req_reduce || forced(c);
-          if (!fire && globaltimer_ns() > c.deadline) {
-            note_timeout(c);
-            fire = true;
-          }
-          if (fire) {  // first CTA to see the threshold met fixes the contributor set of the chunk
+            if (ld_volatile(arr + s * cpb + ch) == c.tag) have |= 1u << s;
+          if (__popc(have) >= p.a.req_reduce || give_up(c, spins, c.deadline)) {
+            // first CTA to see the threshold met (or to give up) fixes the contributor set of the chunk
             const uint32_t old = atomicCAS(red_mask + ch, 0u, have | kDecided);
             m = (old & kDecided) ? old : (have | kDecided);
             break;
           }
-          __nanosleep(32);
+          __nanosleep(100);
           m = ld_volatile(red_mask + ch);
         }
         m &= ~kDecided;
         for (int s = 0; s < P; ++s)  // acquire every contributor's data on this SM
           if ((m >> s) & 1u) (void)ld_acquire_sys(arr + s * cpb + ch);
         sh_word = m;
+        if (trace != nullptr) wait_r += globaltimer_ns() - w0;
       }
       if (threadIdx.x < P) {
         const int q = (threadIdx.x + c.rank) % P;
@@ -575,21 +654,16 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       }
       __syncthreads();
       if (threadIdx.x == 0) {
-        __threadfence_system();
-        if (atomicAdd(red_cnt + ch, 1u) == static_cast<uint32_t>(ntiles - 1)) {  // ReduceBlock sent
-          st_volatile(red_cnt + ch, 0u);
-          st_volatile(red_mask + ch, 0u);
-          __threadfence_system();
-          const uint64_t f = (static_cast<uint64_t>(c.tag) << 32) | static_cast<uint32_t>(cnt);
-          for (int i = 0; i < P; ++i) {
-            const int q = (i + c.rank) % P;
-            if ((dest_ok >> q) & 1u)
-              st_release_sys(reinterpret_cast<uint64_t*>(p.a.sym[q] + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
-          }
-        }
+        __threadfence();
+        atomicAdd(red_cnt + ch, 1u);
       }
     }
   }
+  if (threadIdx.x == 0) {  // tells the publisher that this CTA will add nothing more to the S and R counters
+    __threadfence();
+    atomicAdd(reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_fin_cnt) + 3, 1u);
+  }
+  if (trace != nullptr && threadIdx.x == 0) trace[3] = globaltimer_ns();
 
   // ---- phase C: assemble output + counts as reduced chunks are acknowledged ----
   {
@@ -612,6 +686,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
       const int idx = o * cpb + ch;
       if (threadIdx.x == 0) {
+        const uint64_t w0 = trace != nullptr ? globaltimer_ns() : 0;
         bool present = false;
         for (;;) {
           if ((ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u) {
@@ -632,6 +707,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
         if (present) cnt = static_cast<int>(static_cast<uint32_t>(ld_acquire_sys(rflag + idx)));
         sh_word = present ? 1u : 0u;
         sh_cnt = cnt;
+        if (trace != nullptr) wait_c += globaltimer_ns() - w0;
       }
       __syncthreads();
       const bool present = sh_word != 0;
@@ -657,7 +733,15 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) finish_cta(p, c);
+  if (threadIdx.x == 0) {
+    if (trace != nullptr) {
+      trace[4] = globaltimer_ns();
+      trace[5] = wait_r;
+      trace[6] = wait_c;
+      trace[7] = pub_s;
+    }
+    finish_cta(p, c);
+  }
 }
 
 template <typename TIn, typename TW, bool kNvls>
@@ -671,6 +755,7 @@ __global__ void __launch_bounds__(kThreads, 1) aar_twoshot_kernel(const __grid_c
   c.my_sym = p.a.sym[c.rank];
   c.scratch = p.a.scratch[c.vr];
   c.host = p.a.host_flags != nullptr ? p.a.host_flags + 4 * c.vr : nullptr;
+  c.force = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_fin_cnt) + 2;
   c.deadline = globaltimer_ns() + p.a.timeout_ns;
   if (blockIdx.x == 0) control_cta(p, c);
   else work_cta<TIn, TW, kNvls>(p, c);
@@ -735,6 +820,11 @@ int64_t aar_sym_flag_bytes(int64_t n, int64_t max_chunk, int world, int L, int w
 int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block_step) {
   const SymLayout s = SymLayout::make(n, max_chunk, world, 1, 4, 0, block_step);
   return ScratchLayout::make(world, s.cpb).total_bytes;
+}
+
+int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_t block_step) {
+  const SymLayout s = SymLayout::make(n, max_chunk, world, 1, 4, 0, block_step);
+  return ScratchLayout::make(world, s.cpb).off_fin_cnt + 8;
 }
 
 int aar_max_emu_ctas(int world, int device) {

@@ -81,7 +81,9 @@ struct ScratchLayout {
   int64_t off_scat_cnt;   // u32 [P][cpb]   tiles of (dest, chunk) already pushed
   int64_t off_red_cnt;    // u32 [cpb]      tiles of my chunk already reduced + broadcast
   int64_t off_red_mask;   // u32 [cpb]      decided contributor mask | kDecided
-  int64_t off_fin_cnt;    // u32 [0] CTAs that finished; [1] decided set of scatter destinations
+  int64_t off_fin_cnt;    // u32 [0] CTAs that finished; [1] decided set of scatter destinations;
+                          //     [2] force tag, written by the HOST (never reset by the kernel);
+                          //     [3] work CTAs that are past phase R
   int64_t off_complete;   // u32 [1 + words] completion decision + snapshot bitmap of (owner, chunk)
   int64_t total_bytes;
 

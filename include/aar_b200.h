@@ -52,9 +52,13 @@ typedef struct AarLaunch {
   uint8_t* sym[AAR_MAX_RANKS];       /* base of every rank's symmetric region */
   uint8_t* mc_base;                  /* NVLS multicast alias of the region, or NULL */
   uint8_t* scratch[AAR_MAX_RANKS];   /* local scratch, aar_scratch_bytes(), zeroed once */
-  volatile uint32_t* host_flags;     /* mapped pinned: [0] force-complete tag (read), [1] done tag,
-                                        [2] timeouts seen (written); 4 words per rank in emulation
-                                        mode; may be NULL */
+  volatile uint32_t* host_flags;     /* mapped pinned, written by the kernel only: [1] done tag, [2] tag of
+                                        the last round closed by a timeout; 4 words per rank in emulation
+                                        mode; may be NULL.  (The force-complete tag is a DEVICE word:
+                                        aar_scratch_force_offset() bytes into each rank's scratch.) */
+  uint64_t* trace;                   /* optional device buffer [ranks][ctas+1][16] of globaltimer stamps
+                                        (start, gate passed, S done, R done, C done, ns waiting in R,
+                                        ns waiting in C, ns publishing in S); NULL = no tracing */
 } AarLaunch;
 
 /* Sizes of the symmetric region / local scratch for a configuration. */
@@ -63,6 +67,9 @@ int64_t aar_sym_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_d
 int64_t aar_sym_flag_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
                            int64_t block_step);
 int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block_step);
+/* Byte offset, inside a rank's scratch, of the u32 force tag: rounds with tag <= that value close
+ * every wait immediately (device form of the catch-up path, AllreduceWorker.scala:100-106). */
+int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_t block_step);
 
 /* Launches one round on `stream` (a cudaStream_t).  Returns the number of kernels launched
  * (>0) or a negative error. */

@@ -16,4 +16,8 @@ def test_all_visible_gpus():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_worker.py")]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
-    assert p.returncode == 0, p.stdout[-4000:] + p.stderr[-4000:]
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "multi_gpu_test.log"), "w") as f:
+        f.write(p.stdout + "\n--- stderr ---\n" + p.stderr)
+    lines = [l for l in (p.stdout + p.stderr).splitlines() if "FAIL" in l or "Error" in l or "error" in l]
+    assert p.returncode == 0, "\n".join(lines[-40:])
