@@ -13,6 +13,8 @@ Rebuilds only when a source or header is newer than the artefact.
 """
 from __future__ import annotations
 
+import fcntl
+import hashlib
 import os
 import shutil
 import subprocess
@@ -43,11 +45,41 @@ CUDA_SOURCES = [
 CUDA_ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 
-def _newer_than(target: Path, deps: list[Path]) -> bool:
-    if not target.exists():
+def _digest(deps: list[Path], extra: str = "") -> str:
+    h = hashlib.sha256(extra.encode())
+    for d in sorted(set(deps)):
+        if d.exists():
+            h.update(str(d.relative_to(ROOT)).encode())
+            h.update(d.read_bytes())
+    return h.hexdigest()
+
+
+def _stale(target: Path, deps: list[Path], extra: str = "") -> bool:
+    """A library is stale when the digest of its sources differs from the one recorded at build time.
+    (Content, not mtimes: a snapshot copied to another machine keeps its libraries.)"""
+    stamp = target.with_suffix(target.suffix + ".srchash")
+    if not target.exists() or not stamp.exists():
         return True
-    t = target.stat().st_mtime
-    return any(d.stat().st_mtime > t for d in deps if d.exists())
+    return stamp.read_text().strip() != _digest(deps, extra)
+
+
+def _record(target: Path, deps: list[Path], extra: str = "") -> None:
+    target.with_suffix(target.suffix + ".srchash").write_text(_digest(deps, extra))
+
+
+class _BuildLock:
+    """One builder at a time per checkout: ranks started together must not write the same .so."""
+
+    def __enter__(self):
+        NATIVE.mkdir(exist_ok=True)
+        self._f = open(NATIVE / ".build.lock", "w")
+        fcntl.flock(self._f, fcntl.LOCK_EX)
+        return self
+
+    def __exit__(self, *exc):
+        fcntl.flock(self._f, fcntl.LOCK_UN)
+        self._f.close()
+        return False
 
 
 def _headers() -> list[Path]:
@@ -74,32 +106,36 @@ def cuda_library_path() -> Path:
 def build_host(force: bool = False) -> Path:
     import pybind11
 
-    NATIVE.mkdir(exist_ok=True)
     out = host_library_path()
     srcs = [CSRC / s for s in HOST_SOURCES]
-    if not force and not _newer_than(out, srcs + _headers()):
+    deps = srcs + _headers()
+    if not force and not _stale(out, deps):
         return out
-    objdir = ROOT / "build" / "host"
-    objdir.mkdir(parents=True, exist_ok=True)
-    common = [
-        "g++", "-std=c++17", "-O2", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-parameter",
-        f"-I{INCLUDE}", f"-I{CSRC / 'host'}", f"-I{pybind11.get_include()}",
-        f"-I{sysconfig.get_paths()['include']}",
-    ]
-    objs = []
-    procs = []
-    for s in srcs:
-        o = objdir / (s.stem + ".o")
-        objs.append(o)
-        if force or _newer_than(o, [s] + _headers()):
+    with _BuildLock():
+        if not force and not _stale(out, deps):  # somebody else built it while we waited
+            return out
+        objdir = ROOT / "build" / "host"
+        objdir.mkdir(parents=True, exist_ok=True)
+        common = [
+            "g++", "-std=c++17", "-O2", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-parameter",
+            f"-I{INCLUDE}", f"-I{CSRC / 'host'}", f"-I{pybind11.get_include()}",
+            f"-I{sysconfig.get_paths()['include']}",
+        ]
+        objs, procs = [], []
+        for s in srcs:
+            o = objdir / (s.stem + ".o")
+            objs.append(o)
             procs.append((s, subprocess.Popen(common + ["-c", str(s), "-o", str(o)],
                                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
-    for s, p in procs:
-        log, _ = p.communicate()
-        if p.returncode != 0:
-            sys.stderr.write(log)
-            raise RuntimeError(f"native build failed compiling {s}")
-    _run(["g++", "-shared", "-o", str(out)] + [str(o) for o in objs] + ["-lpthread"])
+        for s, p in procs:
+            log, _ = p.communicate()
+            if p.returncode != 0:
+                sys.stderr.write(log)
+                raise RuntimeError(f"native build failed compiling {s}")
+        tmp = out.with_suffix(".tmp%d" % os.getpid())
+        _run(["g++", "-shared", "-o", str(tmp)] + [str(o) for o in objs] + ["-lpthread"])
+        os.replace(tmp, out)
+        _record(out, deps)
     return out
 
 
@@ -109,22 +145,28 @@ def nvcc_path() -> str | None:
 
 
 def build_cuda(force: bool = False) -> Path:
-    NATIVE.mkdir(exist_ok=True)
     out = cuda_library_path()
     srcs = [CSRC / s for s in CUDA_SOURCES if (CSRC / s).exists()]
-    if not force and not _newer_than(out, srcs + _headers()):
+    deps = srcs + _headers()
+    if not force and not _stale(out, deps):
         return out
-    nvcc = nvcc_path()
-    if nvcc is None:
-        raise RuntimeError("nvcc not found; cannot build the sm_100a kernels")
-    cmd = [nvcc, "-std=c++17", "-O3", "-lineinfo", *CUDA_ARCH, "-Xcompiler", "-fPIC", "-shared",
-           "-Xptxas", "-v", f"-I{INCLUDE}", f"-I{CSRC / 'cuda'}", "-o", str(out)] + [str(s) for s in srcs]
-    proc = subprocess.run(cmd, capture_output=True, text=True)
-    (ROOT / "build").mkdir(exist_ok=True)
-    (ROOT / "build" / "ptxas_v.log").write_text(proc.stdout + proc.stderr)
-    if proc.returncode != 0:
-        sys.stderr.write(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
-        raise RuntimeError("nvcc failed")
+    with _BuildLock():
+        if not force and not _stale(out, deps):
+            return out
+        nvcc = nvcc_path()
+        if nvcc is None:
+            raise RuntimeError("nvcc not found; cannot build the sm_100a kernels")
+        tmp = out.with_suffix(".tmp%d" % os.getpid())
+        cmd = [nvcc, "-std=c++17", "-O3", "-lineinfo", *CUDA_ARCH, "-Xcompiler", "-fPIC", "-shared",
+               "-Xptxas", "-v", f"-I{INCLUDE}", f"-I{CSRC / 'cuda'}", "-o", str(tmp)] + [str(s) for s in srcs]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        (ROOT / "build").mkdir(exist_ok=True)
+        (ROOT / "build" / "ptxas_v.log").write_text(proc.stdout + proc.stderr)
+        if proc.returncode != 0:
+            sys.stderr.write(" ".join(cmd) + "\n" + proc.stdout + proc.stderr)
+            raise RuntimeError("nvcc failed")
+        os.replace(tmp, out)
+        _record(out, deps)
     return out
 
 

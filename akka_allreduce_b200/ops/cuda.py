@@ -22,7 +22,8 @@ class AarLaunch(C.Structure):
     _fields_ = [
         ("rank", C.c_int32), ("world", C.c_int32), ("emu", C.c_int32),
         ("algo", C.c_int32), ("in_dtype", C.c_int32), ("wire_dtype", C.c_int32),
-        ("ctas", C.c_int32), ("use_tma", C.c_int32),
+        ("ctas", C.c_int32), ("use_tma", C.c_int32), ("fast_fences", C.c_int32),
+        ("role_s", C.c_int32), ("role_c", C.c_int32),
         ("n", C.c_int64), ("max_chunk", C.c_int64), ("os_cap", C.c_int64), ("block_step", C.c_int64),
         ("L", C.c_int32), ("slot", C.c_int32),
         ("tag", C.c_uint32),
@@ -63,6 +64,9 @@ def lib() -> C.CDLL:
     l.aar_sym_bytes.argtypes = [i64, i64, i32, i32, i32, i64, i64]
     l.aar_sym_flag_bytes.restype = i64
     l.aar_sym_flag_bytes.argtypes = [i64, i64, i32, i32, i32, i64, i64]
+    for fn in (l.aar_sym_scat_offset, l.aar_sym_sink_offset):
+        fn.restype = i64
+        fn.argtypes = [i64, i64, i32, i32, i32, i64, i64]
     l.aar_scratch_bytes.restype = i64
     l.aar_scratch_bytes.argtypes = [i64, i64, i32, i64]
     l.aar_scratch_force_offset.restype = i64

@@ -51,6 +51,9 @@ class RoundLauncher:
                                                 geo.block_step_arg)
         self.flag_bytes = self.lib.aar_sym_flag_bytes(geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code,
                                                       os_cap, geo.block_step_arg)
+        layout_args = (geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code, os_cap, geo.block_step_arg)
+        self.off_scat = self.lib.aar_sym_scat_offset(*layout_args)
+        self.off_sink = self.lib.aar_sym_sink_offset(*layout_args)
         self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.force_offset = self.lib.aar_scratch_force_offset(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.launches = 0
@@ -61,6 +64,9 @@ class RoundLauncher:
         a.world, a.algo = g.world, self.algo
         a.in_dtype, a.wire_dtype = self.in_code, self.wire_code
         a.ctas, a.use_tma = self.ctas, 0 if os.environ.get("AAR_NO_TMA") else 1
+        a.fast_fences = 1 if os.environ.get("AAR_FAST_FENCES") else 0
+        a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
+        a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate
@@ -105,7 +111,7 @@ class EmulatedCluster:
                  wire_dtype=None, th_reduce: float = 1.0, th_complete: float = 1.0,
                  th_allreduce: float | None = None, ctas: int | None = None, align_blocks: bool = False,
                  timeout_ms: float = 2000.0, scale: float = 1.0, normalize: bool = False,
-                 device: str | torch.device = "cuda:0"):
+                 device: str | torch.device = "cuda:0", algo: str = "twoshot"):
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
@@ -113,8 +119,11 @@ class EmulatedCluster:
         lib = K.lib()
         cap = K.check(lib.aar_max_emu_ctas(world, self.device.index or 0), "aar_max_emu_ctas")
         want = ctas or default_ctas(n * torch.empty((), dtype=dtype).element_size())
+        if algo not in ("twoshot", "oneshot"):
+            raise ValueError("the emulated cluster runs the two-shot and one-shot kernels (NVLS needs real peers)")
         self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
-                                      max(1, min(want, cap)), timeout_ms, scale, normalize)
+                                      max(1, min(want, cap)), timeout_ms, scale, normalize,
+                                      os_cap=n if algo == "oneshot" else 0, algo=K.ALGO_NAMES[algo])
         L = self.launcher
         self.world = world
         self.sym = torch.zeros(world, L.sym_bytes, dtype=torch.uint8, device=self.device)

@@ -21,11 +21,27 @@ from ..ops.fused_allreduce import Injection, RoundLauncher
 from ..ops.geometry import Geometry, default_ctas
 
 
+def oneshot_eligible(geo: Geometry, th_reduce: float, th_complete: float, max_lag: int, th_allreduce) -> bool:
+    full = geo.req_reduce(th_reduce) >= geo.world and geo.req_complete(th_complete) >= geo.total_chunks
+    return full and (max_lag >= 1 or th_allreduce is not None)
+
+
 def default_uds_dir(tag: str | int | None = None) -> str:
     tag = tag if tag is not None else os.environ.get("MASTER_PORT", "0")
     d = os.path.join(tempfile.gettempdir(), f"aar_b200_{os.getuid()}_{tag}")
     os.makedirs(d, exist_ok=True)
     return d
+
+
+class _DevicePointer:
+    """Minimal __cuda_array_interface__ holder so torch can wrap a raw device address."""
+
+    _TYPESTR = {torch.float32: "<f4", torch.bfloat16: "<u2", torch.int32: "<i4"}
+
+    def __init__(self, ptr: int, numel: int, dtype: torch.dtype):
+        self.dtype = dtype
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": self._TYPESTR[dtype], "data": (ptr, False),
+                                         "version": 3, "strides": None}
 
 
 class DeviceAllreduce:
@@ -42,11 +58,19 @@ class DeviceAllreduce:
         self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
         wire = wire_dtype or dtype
         elem = torch.empty((), dtype=dtype).element_size()
-        self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
-                                      ctas or default_ctas(n * elem), timeout_ms, scale, normalize)
-        lib = self.launcher.lib
-        if algo not in ("auto", "twoshot", "nvls"):
+        if algo not in ("auto", "twoshot", "nvls", "oneshot"):
             raise ValueError(f"unknown algo {algo!r}")
+        # One-shot (every rank sums all P copies itself) is the latency path for small messages; it needs
+        # thresholds of 1 (ranks reduce independently, so they must all see the same contributors).
+        oneshot_ok = oneshot_eligible(self.geo, th_reduce, th_complete, max_lag, th_allreduce)
+        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", 256 << 10))
+        if algo == "oneshot" and not oneshot_ok:
+            raise K.AarError("algo=oneshot needs thReduce = thComplete = 1 and maxLag >= 1 (or the thAllreduce gate)")
+        use_oneshot = algo == "oneshot" or (algo == "auto" and oneshot_ok and small and world > 1)
+        self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
+                                      ctas or default_ctas(n * elem), timeout_ms, scale, normalize,
+                                      os_cap=n if use_oneshot else 0)
+        lib = self.launcher.lib
         self._heap = C.c_void_p()
         K.check(lib.aar_heap_create(C.byref(self._heap), rank, world, self.device_index, self.launcher.sym_bytes,
                                     (uds_dir or default_uds_dir()).encode(), int(multicast)), "aar_heap_create")
@@ -57,10 +81,15 @@ class DeviceAllreduce:
         self.mc_ptr = mc.value  # None when the driver exposes no multicast
         # NVLS reduces inside the switch over ALL ranks, so it is only eligible when no contribution may be
         # left out (thReduce = 1); chunks that time out fall back to unicast pulls inside the same kernel.
-        nvls_ok = bool(self.mc_ptr) and world > 1 and self.launcher.req_reduce >= world
-        if algo == "nvls" and not nvls_ok:
+        nvls_ok = bool(self.mc_ptr) and world > 2 and self.launcher.req_reduce >= world  # at 2 ranks push moves the same bytes
+        if algo == "nvls" and not (bool(self.mc_ptr) and world > 1 and self.launcher.req_reduce >= world):
             raise K.AarError("algo=nvls needs a multicast alias (NVLS), world > 1 and thReduce = 1")
-        self.algo = "nvls" if (algo == "nvls" or (algo == "auto" and nvls_ok and os.environ.get("AAR_NO_NVLS") is None)) else "twoshot"
+        if use_oneshot:
+            self.algo = "oneshot"
+        elif algo == "nvls" or (algo == "auto" and nvls_ok and os.environ.get("AAR_NO_NVLS") is None):
+            self.algo = "nvls"
+        else:
+            self.algo = "twoshot"
         self.launcher.algo = K.ALGO_NAMES[self.algo]
         self.scratch = torch.zeros(self.launcher.scratch_bytes, dtype=torch.uint8, device=self.device)
         self.host_flags = torch.zeros(4, dtype=torch.int32).pin_memory()
@@ -77,6 +106,42 @@ class DeviceAllreduce:
             a.sym[i] = self.peer_ptrs[i]
         a.mc_base = self.mc_ptr
         a.host_flags = self.host_flags.data_ptr()
+
+    # ---- zero-copy buffers ---------------------------------------------------------------------
+    def _view(self, byte_offset: int, numel: int) -> torch.Tensor:
+        dt = self.launcher.wire_dtype
+        holder = _DevicePointer(self.peer_ptrs[self.rank] + byte_offset, numel, dt)
+        t = torch.as_tensor(holder, device=self.device)
+        return t.view(torch.bfloat16) if dt == torch.bfloat16 else t
+
+    @property
+    def zero_copy_ok(self) -> bool:
+        """True when a round's staging/sink slot has the flat layout of the message (blocks unpadded) and
+        no conversion is needed, so user tensors can alias the symmetric slots."""
+        g, l = self.geo, self.launcher
+        return g.step % 128 == 0 and l.dtype == l.wire_dtype and l.scale == 1.0 and self.algo != "oneshot"
+
+    def input_view(self, round_: int) -> torch.Tensor | None:
+        """Tensor aliasing the staging slot of ``round_`` (NVLS mode only: there the scatter stages the
+        message locally and the switch pulls it).  A source written here needs no copy at all."""
+        if not (self.zero_copy_ok and self.algo == "nvls"):
+            return None
+        l, g = self.launcher, self.geo
+        esz = torch.empty((), dtype=l.wire_dtype).element_size()
+        slot = round_ % g.slots
+        return self._view(l.off_scat + slot * g.world * g.step * esz, g.n)
+
+    def output_view(self, round_: int) -> torch.Tensor | None:
+        """Tensor aliasing the sink slot of ``round_``: the reduced message lands here anyway, so using it
+        as ``out`` skips the flush copy.  Valid until the slot is recycled ``maxLag + 1`` rounds later.
+        Only handed out when no chunk can be missing (thComplete = 1): a straggler's late push could
+        otherwise overwrite zeros the caller was told about."""
+        l, g = self.launcher, self.geo
+        if not self.zero_copy_ok or l.req_complete < g.total_chunks:
+            return None
+        esz = torch.empty((), dtype=l.wire_dtype).element_size()
+        slot = round_ % g.slots
+        return self._view(l.off_sink + slot * g.world * g.step * esz, g.n)
 
     @property
     def has_multicast(self) -> bool:
@@ -110,16 +175,27 @@ class DeviceAllreduce:
         return self.trace
 
     def trace_summary(self) -> dict:
+        """Phase timeline of the last traced launch, in microseconds from the first CTA's start, per role
+        (role 0 = CTA runs all phases, 1 = scatter, 2 = reduce+broadcast, 3 = complete)."""
         torch.cuda.synchronize(self.device)
         t = self.trace[1:].cpu().double()  # work CTAs only (row 0 is the control CTA)
         t0 = float(t[:, 0].min())
         us = lambda x: round(float(x) / 1e3, 1)
-        return {"gate_us": us((t[:, 1] - t0).max()), "S_done_us": [us((t[:, 2] - t0).min()), us((t[:, 2] - t0).max())],
-                "R_done_us": [us((t[:, 3] - t0).min()), us((t[:, 3] - t0).max())],
-                "C_done_us": [us((t[:, 4] - t0).min()), us((t[:, 4] - t0).max())],
-                "wait_in_R_us": [us(t[:, 5].min()), us(t[:, 5].max())], "wait_in_C_us": [us(t[:, 6].min()), us(t[:, 6].max())],
-                "publish_in_S_us": [us(t[:, 7].min()), us(t[:, 7].max())],
-                "S_done_sorted_us": [us(x) for x in sorted((t[:, 2] - t0).tolist())[:: max(1, len(t) // 12)]]}
+        out = {"gate_us": us((t[:, 1] - t0).max()), "end_us": us((t[:, 4] - t0).max())}
+        for role, name, col in ((0, "all", 4), (1, "S", 2), (2, "R", 3), (3, "C", 4)):
+            rows = t[t[:, 8] == role]
+            if len(rows) == 0:
+                continue
+            entry = {"ctas": len(rows), "done_us": [us((rows[:, col] - t0).min()), us((rows[:, col] - t0).max())]}
+            if role in (0, 2):
+                entry["wait_us"] = [us(rows[:, 5].min()), us(rows[:, 5].max())]
+            if role in (0, 3):
+                entry["wait_c_us"] = [us(rows[:, 6].min()), us(rows[:, 6].max())]
+            if role == 0:
+                entry["S_done_us"] = [us((rows[:, 2] - t0).min()), us((rows[:, 2] - t0).max())]
+                entry["R_done_us"] = [us((rows[:, 3] - t0).min()), us((rows[:, 3] - t0).max())]
+            out[name] = entry
+        return out
 
     def force_complete(self, round_: int) -> None:
         """Host side of the catch-up path: any wait of rounds <= ``round_`` closes immediately.  The tag

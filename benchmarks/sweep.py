@@ -47,6 +47,8 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--algo", default="auto")
+    ap.add_argument("--zero-copy", action="store_true", help="source/sink tensors alias the engine's symmetric slots")
+    ap.add_argument("--no-counts", action="store_true")
     ap.add_argument("--trace", action="store_true", help="print per-phase device timestamps of one extra round")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -102,6 +104,7 @@ def main():
                     ms = timed(lambda i: cl.run_round(srcs), args.iters, args.warmup)
                     used = cl.launcher.ctas
                     algo_used = "twoshot"
+                    zc = False
                     del cl, srcs
                 else:
                     from akka_allreduce_b200.parallel.engine import DeviceAllreduce, default_uds_dir
@@ -111,21 +114,39 @@ def main():
                     srcs = [torch.randn(n, device=dev).to(dtype) for _ in range(nsrc)]
                     outs = [torch.empty(n, dtype=dtype, device=dev) for _ in range(2)]
                     cnts = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(2)]
-                    ms = timed(lambda i: eng.allreduce(srcs[i % nsrc], outs[i % 2], cnts[i % 2]), args.iters, args.warmup)
+                    zc = False
+                    if args.zero_copy and eng.output_view(0) is not None:
+                        zc = True
+                        L = eng.geo.slots
+                        outs = [eng.output_view(r) for r in range(L)]
+                        ins = [eng.input_view(r) for r in range(L)]
+                        for r in range(L):
+                            if ins[r] is not None:
+                                ins[r].copy_(srcs[r % nsrc])
+                            else:
+                                ins[r] = srcs[r % nsrc]
+                        srcs, nsrc = ins, L
+                    if args.no_counts:
+                        cnts = [None, None]
+                    if zc:
+                        ms = timed(lambda i: eng.allreduce(srcs[eng.round % nsrc], outs[eng.round % nsrc], cnts[i % 2]), args.iters, args.warmup)
+                    else:
+                        ms = timed(lambda i: eng.allreduce(srcs[i % nsrc], outs[i % 2], cnts[i % 2]), args.iters, args.warmup)
                     used = eng.launcher.ctas
                     algo_used = eng.algo
                     if args.trace:
                         eng.enable_trace()
                         if world > 1:
                             dist.barrier()
-                        eng.allreduce(srcs[0], outs[0], cnts[0])
+                        eng.allreduce(srcs[eng.round % nsrc] if zc else srcs[0], outs[eng.round % nsrc] if zc else outs[0], cnts[0])
                         print(f"[rank {rank}] trace bytes={n * esz} algo={algo_used}: {json.dumps(eng.trace_summary())}", flush=True)
                     eng.close()
                     del srcs, outs, cnts
                 alg = n * esz / (ms * 1e-3) / 1e9
                 row = {"bytes": n * esz, "chunk_bytes": mc * esz, "workers": P, "gpus": world, "ctas": used,
                        "ms": round(ms, 5), "algbw_GBps": round(alg, 2), "busbw_GBps": round(alg * 2 * (P - 1) / P, 2),
-                       "emulated": bool(args.emulate), "dtype": args.dtype, "algo": algo_used}
+                       "emulated": bool(args.emulate), "dtype": args.dtype, "algo": algo_used,
+                       "zero_copy": bool(args.zero_copy) and not args.emulate and zc, "counts": not args.no_counts}
                 if nccl_ms is not None:
                     row["nccl_ms"] = round(nccl_ms, 5)
                     row["nccl_busbw_GBps"] = round(n * esz / (nccl_ms * 1e-3) / 1e9 * 2 * (P - 1) / P, 2)

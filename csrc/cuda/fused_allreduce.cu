@@ -48,6 +48,8 @@ struct KParams {
   Partition part;
   int part_s, tpc_s;  // scatter/complete phases: elements per work item, items per full chunk
   int part_r, tpc_r;  // reduce phase: elements per work item, items per full chunk
+  int part_c, tpc_c;  // complete phase
+  int n_s, n_r, n_c;  // work CTAs per role (scatter / reduce+broadcast / complete); 0,0,0 = every CTA does all three
   int total_chunks;   // reduced chunks that exist this round (empty trailing blocks excluded)
   int vec_ok;         // 16-byte paths usable (alignment of pointers, step and chunk size)
 };
@@ -308,7 +310,7 @@ __device__ __forceinline__ void wait_gate(const KParams& p, const Ctx& c) {
     if (give_up(c, spins, c.deadline)) return;
     __nanosleep(64);
   }
-  __threadfence_system();  // acquire side of the peers' CompleteAllreduce
+  __threadfence();  // acquire side of the peers' CompleteAllreduce
 }
 
 // All CTAs of a rank report here; the last one resets the scratch and publishes completion.
@@ -323,7 +325,7 @@ __device__ __forceinline__ void finish_cta(const KParams& p, const Ctx& c) {
   uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
   const int words = (c.P * p.sym.cpb + 31) / 32;
   for (int i = 0; i < 4 + words; ++i) st_volatile(cw + i, 0u);
-  __threadfence_system();
+  __threadfence();  // nothing but flags follows: the data of this round was fenced when its flags were raised
   for (int i = 0; i < c.P; ++i) {  // CompleteAllreduce(rank, round) to everyone (AllreduceWorker.scala:276)
     const int q = (i + c.rank) % c.P;
     st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + c.rank, c.tag);
@@ -332,11 +334,16 @@ __device__ __forceinline__ void finish_cta(const KParams& p, const Ctx& c) {
 }
 
 // ---------------------------------------------------------------- control CTA
-// Publisher warp: the only place flags leave this rank.  Data CTAs just bump a local counter per
-// (destination, chunk) behind a gpu-scope fence; this warp polls the counters, and whenever some chunks
-// have all their parts in it pays ONE system-scope fence for the whole batch and then raises their flags
-// on the peers.  (A system-scope fence waits for the NVLink traffic of the whole GPU to drain — tens of
-// microseconds under load, see profiles/fence_probe.md — so data CTAs must never sit in one.)
+// Publisher warp: the only place flags leave this rank.  Data CTAs bump a local counter per
+// (destination, chunk) behind a gpu-scope fence — which, for stores that went to a peer, returns only
+// once the peer has acknowledged them; this warp polls the counters and raises the flags of every chunk
+// that has all its parts in: one scan, one fence, then all the flag stores.
+//
+// A system-scope fence on this machine waits for the NVLink traffic of the WHOLE GPU to drain (tens of
+// microseconds while a round is streaming; measured in profiles/fence_probe.md), which is why it is paid
+// here, once per batch, and never by a data CTA.  `fast_fences` (AAR_FAST_FENCES=1, experiments only)
+// downgrades it to gpu scope; that was observed to let a flag overtake multimem.st data on 8 GPUs.
+constexpr int kPubWords = 8;  // up to 256 (destination, chunk) + chunk entries per scan
 __device__ void publisher_warp(const KParams& p, const Ctx& c) {
   const int lane = threadIdx.x & 31;
   const int P = c.P, cpb = p.sym.cpb;
@@ -350,31 +357,49 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
   bool last_pass = false;
   for (;;) {
     const bool closing = ld_volatile(fin + 3) >= static_cast<uint32_t>(p.a.ctas);  // read BEFORE the scan
-    for (int base = 0; base < entries; base += 32) {
-      const int e = base + lane;
-      bool ready = false;
-      int d = 0, ch = 0;
-      if (e < s_entries) {  // ScatterBlock (d, ch): all parts pushed?
-        d = e / cpb;
-        ch = e % cpb;
-        const int64_t bs = p.part.size(d);
-        if (ch < num_chunks(bs, p.a.max_chunk)) {
-          const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s));
-          ready = ld_volatile(scat_cnt + e) == static_cast<uint32_t>(want);
+    for (int base0 = 0; base0 < entries; base0 += 32 * kPubWords) {
+      uint32_t mine = 0;  // bit w: entry base0 + 32*w + lane is complete and unpublished
+#pragma unroll
+      for (int w = 0; w < kPubWords; ++w) {
+        const int e = base0 + 32 * w + lane;
+        bool ready = false;
+        if (e < s_entries) {  // ScatterBlock (d, ch): all parts out?
+          const int d = e / cpb, ch = e % cpb;
+          const int64_t bs = p.part.size(d);
+          if (ch < num_chunks(bs, p.a.max_chunk)) {
+            const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s));
+            ready = ld_volatile(scat_cnt + e) == static_cast<uint32_t>(want);
+          }
+        } else if (e < entries) {  // ReduceBlock (me, ch): all parts reduced and broadcast?
+          const int ch = e - s_entries;
+          if (ch < num_chunks(my_bsize, p.a.max_chunk)) {
+            const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, my_bsize) - chunk_begin(ch, p.a.max_chunk, my_bsize), p.part_r));
+            ready = ld_volatile(red_cnt + ch) == static_cast<uint32_t>(want);
+          }
         }
-      } else if (e < entries) {  // ReduceBlock (me, ch): all parts reduced and broadcast?
-        ch = e - s_entries;
-        if (ch < num_chunks(my_bsize, p.a.max_chunk)) {
-          const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, my_bsize) - chunk_begin(ch, p.a.max_chunk, my_bsize), p.part_r));
-          ready = ld_volatile(red_cnt + ch) == static_cast<uint32_t>(want);
-        }
+        if (ready) mine |= 1u << w;
       }
-      if (__any_sync(0xffffffffu, ready)) {
-        __threadfence_system();  // one fence for every chunk of this batch
-        if (ready && e < s_entries) {
+      if (!__any_sync(0xffffffffu, mine != 0)) continue;
+      // Data that left this GPU (pushed scatter slices, broadcast results — unicast or multimem.st) must
+      // have landed on the peers before its flag does: that takes a system-scope fence.  Slices that were
+      // only staged locally (NVLS scatter) are ordered by a gpu-scope fence: the peers read them through
+      // this GPU's L2.
+      bool remote = false;
+#pragma unroll
+      for (int w = 0; w < kPubWords; ++w)
+        if ((mine >> w) & 1u) remote = remote || !(p.a.algo == AAR_ALGO_NVLS && base0 + 32 * w + lane < s_entries);
+      if (__any_sync(0xffffffffu, remote) && !p.a.fast_fences) __threadfence_system();
+      else __threadfence();
+#pragma unroll
+      for (int w = 0; w < kPubWords; ++w) {
+        if (!((mine >> w) & 1u)) continue;
+        const int e = base0 + 32 * w + lane;
+        if (e < s_entries) {
+          const int d = e / cpb, ch = e % cpb;
           st_volatile(scat_cnt + e, 0u);
           st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
-        } else if (ready) {
+        } else {
+          const int ch = e - s_entries;
           const uint32_t mask = ld_volatile(red_mask + ch) & ~kDecided;
           const uint32_t dest_ok = ld_volatile(fin + 1) & ~kDecided;
           st_volatile(red_cnt + ch, 0u);
@@ -390,7 +415,7 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
     }
     if (last_pass) break;
     if (closing) last_pass = true;  // every work CTA is past phase R: one more scan picks up the rest
-    else __nanosleep(40);
+    else __nanosleep(20);
   }
   if (lane == 0) finish_cta(p, c);
 }
@@ -511,6 +536,18 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   const int P = c.P;
   const int cpb = p.sym.cpb;
   const int wid = blockIdx.x - 1;
+  // Role of this CTA.  With enough CTAs the three phases run CONCURRENTLY on disjoint CTA groups and
+  // the round is pipelined chunk by chunk: scatter feeds HBM/NVLink, reduce+broadcast is NVLink-bound,
+  // completion is HBM-bound, and the flags between them are the only coupling.  With few CTAs (small
+  // messages) every CTA walks through all three phases in order.
+  const bool split = p.n_s > 0;
+  const bool do_s = !split || wid < p.n_s;
+  const bool do_r = !split || (wid >= p.n_s && wid < p.n_s + p.n_r);
+  const bool do_c = !split || wid >= p.n_s + p.n_r;
+  const int s_idx = wid, s_stride = split ? p.n_s : p.a.ctas;
+  // (indices are clamped to 0 for CTAs outside the role: their item count is 0, so the loops do not run)
+  const int r_idx = split ? max(wid - p.n_s, 0) : wid, r_stride = split ? p.n_r : p.a.ctas;
+  const int c_idx = split ? max(wid - p.n_s - p.n_r, 0) : wid, c_stride = split ? p.n_c : p.a.ctas;
   const bool vec = p.vec_ok != 0;
   const bool tma = vec && p.a.use_tma != 0;
   const TIn* src = static_cast<const TIn*>(p.a.src[c.vr]);
@@ -557,8 +594,8 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   {
     const bool pure_copy = tma && sizeof(TIn) == sizeof(TW) && p.a.scale == 1.0f;
     const int tile = p.part_s, tpc = p.tpc_s;
-    const int items = cpb * P * tpc;
-    for (int item = wid; item < items; item += p.a.ctas) {
+    const int items = do_s ? cpb * P * tpc : 0;
+    for (int item = s_idx; item < items; item += s_stride) {
       const int k = item % tpc;
       const int d = ((item / tpc) % P + c.rank) % P;
       const int ch = item / (tpc * P);
@@ -573,7 +610,9 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       TW* dst = kNvls ? reinterpret_cast<TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, d) + off
                       : reinterpret_cast<TW*>(p.a.sym[d] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off;
       const TIn* from = src + p.part.start(d) + off;
-      if (pure_copy && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
+      if (reinterpret_cast<const void*>(from) == reinterpret_cast<const void*>(dst)) {
+        // zero-copy source: the caller produced its message straight into this round's staging slot
+      } else if (pure_copy && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
         if (threadIdx.x == 0)
           tma_copy(ring, reinterpret_cast<uint8_t*>(dst), reinterpret_cast<const uint8_t*>(from),
                    static_cast<int64_t>(len) * sizeof(TW), nullptr, sizeof(TW));
@@ -597,8 +636,8 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     const int nch = num_chunks(bsize, p.a.max_chunk);
     const uint32_t* arr = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_arr) + p.sym.arr_index(c.slot, 0, 0);
     const int tile = p.part_r, tpc = p.tpc_r;
-    const int items = nch * tpc;
-    for (int item = wid; item < items; item += p.a.ctas) {
+    const int items = do_r ? nch * tpc : 0;
+    for (int item = r_idx; item < items; item += r_stride) {
       const int k = item % tpc;
       const int ch = item / tpc;
       const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
@@ -624,8 +663,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
           m = ld_volatile(red_mask + ch);
         }
         m &= ~kDecided;
-        for (int s = 0; s < P; ++s)  // acquire every contributor's data on this SM
-          if ((m >> s) & 1u) (void)ld_acquire_sys(arr + s * cpb + ch);
+        __threadfence();  // acquire side: the contributors' data is read from L2 / the switch, never from L1
         sh_word = m;
         if (trace != nullptr) wait_r += globaltimer_ns() - w0;
       }
@@ -671,9 +709,9 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
     const uint32_t* bitmap = cw + 4;
     const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + p.sym.arr_index(c.slot, 0, 0);
     const bool pure_copy = tma && sizeof(TIn) == sizeof(TW);
-    const int tile = p.part_s, tpc = p.tpc_s;
-    const int items = cpb * P * tpc;
-    for (int item = wid; item < items; item += p.a.ctas) {
+    const int tile = p.part_c, tpc = p.tpc_c;
+    const int items = do_c ? cpb * P * tpc : 0;
+    for (int item = c_idx; item < items; item += c_stride) {
       const int k = item % tpc;
       const int o = ((item / tpc) % P + c.rank) % P;
       const int ch = item / (tpc * P);
@@ -704,7 +742,10 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
           __nanosleep(64);
         }
         int cnt = 0;
-        if (present) cnt = static_cast<int>(static_cast<uint32_t>(ld_acquire_sys(rflag + idx)));
+        if (present) {
+          cnt = static_cast<int>(static_cast<uint32_t>(ld_volatile64(rflag + idx)));
+          __threadfence();
+        }
         sh_word = present ? 1u : 0u;
         sh_cnt = cnt;
         if (trace != nullptr) wait_c += globaltimer_ns() - w0;
@@ -714,7 +755,16 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       const int cnt = sh_cnt;
       const TW* sink = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, o) + off;
       const int64_t g = p.part.start(o) + off;
-      if (pure_copy && present && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
+      if (present && reinterpret_cast<const void*>(sink) == reinterpret_cast<const void*>(out + g)) {
+        // zero-copy sink: `out` IS this round's sink slot; only the contributor counts are left to write
+        if (counts != nullptr) {
+          int4* cp = reinterpret_cast<int4*>(counts + g);
+          const bool c16 = (reinterpret_cast<uintptr_t>(counts + g) & 15u) == 0;
+          const int quads = c16 ? len / 4 : 0;
+          for (int i = threadIdx.x; i < quads; i += kThreads) cp[i] = make_int4(cnt, cnt, cnt, cnt);
+          for (int i = quads * 4 + threadIdx.x; i < len; i += kThreads) counts[g + i] = cnt;
+        }
+      } else if (pure_copy && present && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
         if (counts != nullptr && sh_tile_cnt != cnt) {  // (re)fill the shared tile of counts
           int4* ct = reinterpret_cast<int4*>(ring.cnt_tile);
           for (int i = threadIdx.x; i < kStageBytes / 16; i += kThreads) ct[i] = make_int4(cnt, cnt, cnt, cnt);
@@ -739,6 +789,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       trace[5] = wait_r;
       trace[6] = wait_c;
       trace[7] = pub_s;
+      trace[8] = split ? (do_s ? 1 : (do_r ? 2 : 3)) : 0;
     }
     finish_cta(p, c);
   }
@@ -759,6 +810,163 @@ __global__ void __launch_bounds__(kThreads, 1) aar_twoshot_kernel(const __grid_c
   c.deadline = globaltimer_ns() + p.a.timeout_ns;
   if (blockIdx.x == 0) control_cta(p, c);
   else work_cta<TIn, TW, kNvls>(p, c);
+}
+
+// ---------------------------------------------------------------- one-shot (small messages)
+// Latency path for thresholds = 1: every rank pushes its WHOLE message into every peer's one-shot
+// slot, then each rank sums the P copies it holds in peer order.  One NVLink hop instead of two, no
+// owner, no control CTA, no scratch traffic: CTA k owns slice k of the message end to end and has its
+// own arrival flag per sender, so CTAs never talk to each other.  All ranks add the same values in
+// the same order, so they still end up bit-identical (what the owner-reduces rule gives the two-shot
+// path).  A sender that does not show up before the timeout is left out and the count says so.
+template <typename TIn, typename TW>
+__global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_constant__ KParams p) {
+  __shared__ uint32_t sh_mask;
+  const int vr = p.a.emu ? blockIdx.y : 0;
+  const int rank = p.a.emu ? static_cast<int>(blockIdx.y) : p.a.rank;
+  const int P = p.a.world, slot = p.a.slot;
+  const uint32_t tag = p.a.tag;
+  uint8_t* my_sym = p.a.sym[rank];
+  uint8_t* scratch = p.a.scratch[vr];
+  Ctx c;
+  c.rank = rank;
+  c.vr = vr;
+  c.P = P;
+  c.slot = slot;
+  c.tag = tag;
+  c.my_sym = my_sym;
+  c.scratch = scratch;
+  c.host = p.a.host_flags != nullptr ? p.a.host_flags + 4 * vr : nullptr;
+  c.force = reinterpret_cast<const uint32_t*>(scratch + p.scr.off_fin_cnt) + 2;
+  c.deadline = globaltimer_ns() + p.a.timeout_ns;
+  const int nct = gridDim.x;
+  const bool vec = p.vec_ok != 0;
+  // slice of this CTA, in multiples of 8 elements so 16-byte accesses stay aligned
+  const int64_t per = ceil_div(ceil_div(p.a.n, nct), 8) * 8;
+  const int64_t lo = min(static_cast<int64_t>(blockIdx.x) * per, p.a.n);
+  const int64_t hi = min(lo + per, p.a.n);
+  const int len = static_cast<int>(hi - lo);
+  const TIn* src = static_cast<const TIn*>(p.a.src[vr]);
+  TIn* out = static_cast<TIn*>(p.a.out[vr]);
+  int32_t* counts = p.a.counts[vr];
+
+  if (threadIdx.x == 0) {
+    if (p.a.delay_ns[rank] != 0) {
+      const uint64_t until = globaltimer_ns() + p.a.delay_ns[rank];
+      while (globaltimer_ns() < until) __nanosleep(256);
+    }
+    wait_gate(p, c);
+  }
+  __syncthreads();
+  const bool muted = (p.a.mute_mask >> rank) & 1u;
+  const uint32_t skip = p.a.skip_dest_mask[rank];
+
+  // ---- push my slice to every peer (self first), then raise my flag there
+  if (len > 0 && !muted) {
+    for (int i = 0; i < P; ++i) {
+      const int q = (i + rank) % P;
+      if ((skip >> q) & 1u) continue;
+      TW* dst = reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_os) + p.sym.os_elem(slot, rank) + lo;
+      push_tile<TIn, TW>(src + lo, dst, len, p.a.scale, vec);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0 && !muted) {
+    if (p.a.fast_fences) __threadfence();
+    else __threadfence_system();  // the slices must have landed on the peers before the flags do
+    for (int i = 0; i < P; ++i) {
+      const int q = (i + rank) % P;
+      if ((skip >> q) & 1u) continue;
+      st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_os_arr) +
+                         (static_cast<int64_t>(slot) * P + rank) * kMaxOneShotCtas + blockIdx.x,
+                     tag);
+    }
+  }
+
+  // ---- wait for every sender's slice, then reduce locally
+  if (threadIdx.x == 0) {
+    const uint32_t* arr = reinterpret_cast<const uint32_t*>(my_sym + p.sym.off_os_arr) +
+                          static_cast<int64_t>(slot) * P * kMaxOneShotCtas + blockIdx.x;
+    const uint32_t all = (1u << P) - 1u;
+    uint32_t have = 0;
+    int spins = 0;
+    for (;;) {
+      for (int s = 0; s < P; ++s)
+        if (!((have >> s) & 1u) && ld_volatile(arr + s * kMaxOneShotCtas) == tag) have |= 1u << s;
+      if (have == all || __popc(have) >= p.a.req_reduce && p.a.req_reduce < P) break;
+      if (give_up(c, spins, c.deadline)) break;
+    }
+    __threadfence();
+    sh_mask = have;
+  }
+  __syncthreads();
+  const uint32_t mask = sh_mask;
+  const int cnt = __popc(mask);
+  const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
+  if (len > 0) {
+    const TW* row0 = reinterpret_cast<const TW*>(my_sym + p.sym.off_os) + p.sym.os_elem(slot, 0) + lo;
+    constexpr int E = 16 / (sizeof(TIn) > sizeof(TW) ? sizeof(TIn) : sizeof(TW));
+    using UW = Unit<TW, E>;
+    using UO = Unit<TIn, E>;
+    int done = 0;
+    if (vec) {
+      const int units = len / E;
+      for (int u = threadIdx.x; u < units; u += kThreads) {
+        float acc[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[e] = 0.f;
+        for (int s0 = 0; s0 < P; s0 += 8) {
+          typename UW::raw_t r[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int s = s0 + j;
+            if (s < P && ((mask >> s) & 1u))
+              r[j] = ld_fresh(reinterpret_cast<const typename UW::raw_t*>(row0 + static_cast<int64_t>(s) * p.sym.os_cap) + u);
+          }
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int s = s0 + j;
+            if (s < P && ((mask >> s) & 1u)) {
+              float v[E];
+              UW::unpack(r[j], v);
+#pragma unroll
+              for (int e = 0; e < E; ++e) acc[e] += v[e];
+            }
+          }
+        }
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[e] *= post;
+        reinterpret_cast<typename UO::raw_t*>(out + lo)[u] = UO::pack(acc);
+        if (counts != nullptr) {
+          int4* cp = reinterpret_cast<int4*>(counts + lo + static_cast<int64_t>(u) * E);
+#pragma unroll
+          for (int e = 0; e < E / 4; ++e) cp[e] = make_int4(cnt, cnt, cnt, cnt);
+        }
+      }
+      done = units * E;
+    }
+    for (int i = done + threadIdx.x; i < len; i += kThreads) {
+      float acc = 0.f;
+      for (int s = 0; s < P; ++s)
+        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(row0 + static_cast<int64_t>(s) * p.sym.os_cap + i));
+      out[lo + i] = from_float<TIn>(acc * post);
+      if (counts != nullptr) counts[lo + i] = cnt;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {  // last CTA publishes CompleteAllreduce
+    uint32_t* fin = reinterpret_cast<uint32_t*>(scratch + p.scr.off_fin_cnt);
+    __threadfence();
+    if (atomicAdd(fin, 1u) == static_cast<uint32_t>(nct - 1)) {
+      st_volatile(fin, 0u);
+      __threadfence();
+      for (int i = 0; i < P; ++i) {
+        const int q = (i + rank) % P;
+        st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + rank, tag);
+      }
+      if (c.host != nullptr) c.host[1] = tag;
+    }
+  }
 }
 
 // ---------------------------------------------------------------- host side
@@ -792,7 +1000,27 @@ int launch_twoshot(const KParams& kp, cudaStream_t stream) {
 }
 
 template <typename TIn, typename TW>
+int launch_oneshot(const KParams& kp, cudaStream_t stream) {
+  int nct = static_cast<int>(ceil_div(kp.a.n, 4096));
+  if (nct > kp.a.ctas) nct = kp.a.ctas;
+  if (nct > kMaxOneShotCtas) nct = kMaxOneShotCtas;
+  if (nct < 1) nct = 1;
+  dim3 grid(nct, kp.a.emu ? kp.a.world : 1);
+  cudaError_t e;
+  if (kp.a.emu) {
+    void* args[] = {const_cast<KParams*>(&kp)};
+    e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(aar_oneshot_kernel<TIn, TW>), grid, dim3(kThreads), args, 0, stream);
+  } else {
+    aar_oneshot_kernel<TIn, TW><<<grid, kThreads, 0, stream>>>(kp);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("one-shot launch: ") + cudaGetErrorString(e));
+  return 1;
+}
+
+template <typename TIn, typename TW>
 int launch_algo(const KParams& kp, cudaStream_t stream) {
+  if (kp.a.algo == AAR_ALGO_ONESHOT) return launch_oneshot<TIn, TW>(kp, stream);
   if (kp.a.algo == AAR_ALGO_NVLS) return launch_twoshot<TIn, TW, true>(kp, stream);
   return launch_twoshot<TIn, TW, false>(kp, stream);
 }
@@ -816,6 +1044,14 @@ int64_t aar_sym_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_d
 int64_t aar_sym_flag_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
                            int64_t block_step) {
   return SymLayout::make(n, max_chunk, world, L, wire_bytes_of(wire_dtype), os_cap, block_step).flags_bytes();
+}
+int64_t aar_sym_scat_offset(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                            int64_t block_step) {
+  return SymLayout::make(n, max_chunk, world, L, wire_bytes_of(wire_dtype), os_cap, block_step).off_scat;
+}
+int64_t aar_sym_sink_offset(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                            int64_t block_step) {
+  return SymLayout::make(n, max_chunk, world, L, wire_bytes_of(wire_dtype), os_cap, block_step).off_sink;
 }
 int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block_step) {
   const SymLayout s = SymLayout::make(n, max_chunk, world, 1, 4, 0, block_step);
@@ -857,8 +1093,18 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
   // about two items per CTA; flags stay per chunk, a self-resetting counter tells the last part to raise it.
   const int64_t sweep = static_cast<int64_t>(kThreads) * kUnitsPerThread * unit_elems;
   const int64_t chunk_len = a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1);
-  auto split = [&](int64_t items_without_split, int& part, int& tpc) {
-    int64_t want = ceil_div(2 * static_cast<int64_t>(a->ctas), items_without_split > 0 ? items_without_split : 1);
+  // Optional role split (see work_cta).
+  kp.n_s = kp.n_r = kp.n_c = 0;
+  // (Measured on 2 and 8 B200s: one CTA keeps at most ~160 KB in flight, so a phase needs most of the
+  // SMs to reach HBM or NVLink speed and splitting the grid three ways loses more than the overlap
+  // gains.  The split therefore only happens on request: role_s / role_c > 0.)
+  if (a->role_s > 0 && a->role_c > 0 && a->role_s + a->role_c < a->ctas && a->algo != AAR_ALGO_ONESHOT) {
+    kp.n_s = a->role_s;
+    kp.n_c = a->role_c;
+    kp.n_r = a->ctas - kp.n_s - kp.n_c;
+  }
+  auto split = [&](int64_t items_without_split, int ctas_of_role, int& part, int& tpc) {
+    int64_t want = ceil_div(2 * static_cast<int64_t>(ctas_of_role), items_without_split > 0 ? items_without_split : 1);
     const int64_t most = ceil_div(chunk_len, sweep);
     if (want > most) want = most;
     if (want < 1) want = 1;
@@ -866,8 +1112,9 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
     part = static_cast<int>(len);
     tpc = static_cast<int>(ceil_div(chunk_len, len));
   };
-  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.part_s, kp.tpc_s);
-  split(kp.sym.cpb, kp.part_r, kp.tpc_r);
+  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.n_s > 0 ? kp.n_s : a->ctas, kp.part_s, kp.tpc_s);
+  split(kp.sym.cpb, kp.n_r > 0 ? kp.n_r : a->ctas, kp.part_r, kp.tpc_r);
+  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.n_c > 0 ? kp.n_c : a->ctas, kp.part_c, kp.tpc_c);
   // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
   const int64_t align_elems = 16 / (in_bytes < wb ? in_bytes : wb);
   bool vec = (kp.sym.block % align_elems == 0) && (a->max_chunk % align_elems == 0 || a->max_chunk >= kp.sym.block);
@@ -884,8 +1131,12 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
   if (a->algo == AAR_ALGO_NVLS) {
     if (a->mc_base == nullptr || a->emu) return fail(AAR_EUNSUPPORTED, "NVLS needs a multicast alias of the symmetric region");
     if (a->req_reduce < a->world) return fail(AAR_EINVAL, "NVLS reduces in the switch over all ranks: thReduce must be 1");
+  } else if (a->algo == AAR_ALGO_ONESHOT) {
+    if (a->n > a->os_cap) return fail(AAR_ETOOBIG, "message larger than the one-shot capacity of the region");
+    if (a->L < 2 && a->gate_count <= 0)
+      return fail(AAR_EINVAL, "one-shot needs maxLag >= 1 or the thAllreduce gate (a peer could overwrite a slot in use)");
   } else if (a->algo != AAR_ALGO_TWOSHOT) {
-    return fail(AAR_EUNSUPPORTED, "algorithm not built into this library yet");
+    return fail(AAR_EUNSUPPORTED, "unknown algorithm");
   }
   if (a->in_dtype == AAR_F32 && a->wire_dtype == AAR_F32) return launch_algo<float, float>(kp, stream);
   if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_algo<__nv_bfloat16, __nv_bfloat16>(kp, stream);

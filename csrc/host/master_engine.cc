@@ -32,18 +32,29 @@ void MasterEngine::terminated(Endpoint worker) {
 
 void MasterEngine::handle(const Message& m) {
   const auto* c = std::get_if<CompleteAllreduce>(&m);
-  if (!c || c->round != round_) return;  // only the current round counts
+  if (!c) return;
+  if (c->round > round_) {
+    // Cannot happen with host-gated workers (they learn of a round from the master).  Device-gated
+    // workers free-run and report asynchronously, so a report may arrive before the master's own
+    // bookkeeping has reached that round: keep it instead of dropping it.
+    early_[c->round] += 1;
+    return;
+  }
+  if (c->round != round_) return;  // only the current round counts; late reports are ignored
   num_complete_ += 1;
-  if (master_gate(num_complete_, cfg_.total_workers, cfg_.th_allreduce)) {
-    if (round_ < cfg_.max_round) {
-      if (verbose_)
-        std::printf("----%d (out of %d) workers complete round %d\n", num_complete_,
-                    cfg_.total_workers, round_);
-      round_ += 1;
-      start_allreduce();
-    } else {
+  while (master_gate(num_complete_, cfg_.total_workers, cfg_.th_allreduce)) {
+    if (round_ >= cfg_.max_round) {
       done_last_ = true;  // rounds 0..max_round inclusive have been run
+      break;
     }
+    if (verbose_)
+      std::printf("----%d (out of %d) workers complete round %d\n", num_complete_, cfg_.total_workers, round_);
+    round_ += 1;
+    start_allreduce();
+    auto it = early_.find(round_);
+    if (it == early_.end()) break;
+    num_complete_ = it->second;
+    early_.erase(it);
   }
 }
 

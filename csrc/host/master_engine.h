@@ -53,6 +53,7 @@ class MasterEngine {
   int round_ = -1;
   int num_complete_ = 0;
   bool done_last_ = false;
+  std::map<int, int> early_;  // completion reports for rounds the master has not started yet
 };
 
 }  // namespace aar

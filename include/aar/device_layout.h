@@ -9,6 +9,8 @@
 //   arr   [L][P][cpb] u32     "ScatterBlock arrived" round tags, written by the sender
 //   rflag [L][P][cpb] u64     "ReduceBlock arrived": round tag << 32 | contributor count
 //   done  [P] u32             CompleteAllreduce: rounds each peer has finished (tag = round+1)
+//   os    [L][P][os_cap]      one-shot path (small messages): every peer's WHOLE message
+//   os_arr[L][P][16] u32      one-shot arrival tags, one per (sender, CTA slice)
 //
 // L = maxLag + 1 ring slots, slot = round % L (buffer/AllReduceBuffer.scala:34-42); P = peers;
 // cpb = chunks per block.  A message is a store into the destination's region followed by a
@@ -22,6 +24,7 @@ namespace aar {
 
 constexpr int kMaxRanks = 16;       // one NVSwitch domain
 constexpr int kAlignElems = 128;    // block padding, in elements (keeps every block 512 B aligned)
+constexpr int kMaxOneShotCtas = 16; // one-shot: every CTA owns a slice and its own arrival flags
 
 struct SymLayout {
   int P, L;
@@ -55,7 +58,7 @@ struct SymLayout {
     s.off_done = off;
     off = up(off + kMaxRanks * 4, 256);
     s.off_os_arr = off;
-    off = up(off + (int64_t)L * P * 4, 4096);
+    off = up(off + (int64_t)L * P * kMaxOneShotCtas * 4, 4096);
     s.off_scat = off;
     off = up(off + (int64_t)L * P * s.block_pad * wire_bytes, 4096);
     s.off_sink = off;

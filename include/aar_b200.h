@@ -32,6 +32,8 @@ typedef struct AarLaunch {
   int32_t wire_dtype;       /* dtype of the symmetric slots */
   int32_t ctas;             /* work CTAs per rank (one control CTA is added) */
   int32_t use_tma;          /* stage tiles with cp.async.bulk when alignment allows */
+  int32_t fast_fences;      /* experiments only: gpu-scope instead of system-scope fences before flags */
+  int32_t role_s, role_c;   /* work CTAs dedicated to the scatter / complete phases; 0 = pick automatically */
   int64_t n, max_chunk;     /* dataSize, maxChunkSize (elements) */
   int64_t os_cap;           /* one-shot capacity the region was laid out with */
   int64_t block_step;       /* 0 = reference partition ceil(n/world); else an aligned step >= that */
@@ -66,6 +68,12 @@ int64_t aar_sym_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_d
                       int64_t block_step);
 int64_t aar_sym_flag_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
                            int64_t block_step);
+/* Byte offsets of the staging (scat) and sink slot arrays inside the region; slot s, row r starts
+ * (s*world + r)*block_pad elements further (block_pad = block step rounded up to 128 elements). */
+int64_t aar_sym_scat_offset(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                            int64_t block_step);
+int64_t aar_sym_sink_offset(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
+                            int64_t block_step);
 int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block_step);
 /* Byte offset, inside a rank's scratch, of the u32 force tag: rounds with tag <= that value close
  * every wait immediately (device form of the catch-up path, AllreduceWorker.scala:100-106). */

@@ -36,7 +36,8 @@ def main() -> int:
     # --- thresholds 1, fp32, several shapes, ring wrap, vs fp32 reference and NCCL
     for n, mc, lag, align, algo in [(1 << 20, 1 << 16, 1, True, "auto"), (1 << 20, 1 << 16, 1, True, "twoshot"),
                                     (778, 3, 3, False, "auto"), (100003, 4096, 2, False, "auto"),
-                                    (100003, 4096, 2, False, "twoshot"), (1 << 22, 1 << 18, 1, False, "auto")]:
+                                    (100003, 4096, 2, False, "twoshot"), (1 << 22, 1 << 18, 1, False, "auto"),
+                                    (256, 256, 1, False, "oneshot"), (50000, 4096, 1, False, "auto")]:
         eng = DeviceAllreduce(rank, world, n, mc, max_lag=lag, th_allreduce=1.0, device=local,
                               uds_dir=default_uds_dir(), align_blocks=align, timeout_ms=20_000, algo=algo)
         out = torch.empty(n, device=dev)

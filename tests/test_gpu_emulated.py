@@ -204,3 +204,28 @@ def test_matches_host_engine_oracle():
     for i in range(world):
         assert np.array_equal(outs[i].cpu().numpy(), got[i][0])
         assert np.array_equal(counts[i].cpu().numpy(), got[i][1])
+
+
+@pytest.mark.parametrize("world,n", [(2, 10), (8, 256), (4, 778), (8, 65536), (5, 100003)])
+def test_oneshot_small_messages(world, n):
+    """One-shot latency path: every rank sums all copies itself; thresholds 1, ring wrap, fp32-exact."""
+    cl = _cluster(world, n, max(1, n // 3), max_lag=1, algo="oneshot", timeout_ms=5000)
+    for r in range(5):
+        srcs = _srcs(world, n, torch.float32, r)
+        outs, counts = cl.run_round(srcs)
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i], want) and bool((counts[i] == world).all())
+    assert cl.timeouts_seen() == [0] * world and cl.done_tags() == [5] * world
+
+
+def test_oneshot_timeout_leaves_out_the_silent_rank():
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    world, n = 4, 4096
+    cl = _cluster(world, n, 1024, algo="oneshot", timeout_ms=20)
+    srcs = _srcs(world, n, torch.float32, 2)
+    outs, counts = cl.run_round(srcs, Injection(mute=1 << 1))
+    want = _ref_sum(srcs, ranks=[0, 2, 3])
+    for i in range(world):
+        assert torch.equal(outs[i], want) and bool((counts[i] == 3).all())
