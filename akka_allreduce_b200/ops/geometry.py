@@ -87,4 +87,4 @@ def default_ctas(message_bytes: int) -> int:
         return 16
     if message_bytes <= 16 << 20:
         return 32
-    return 96
+    return 128  # measured best on 8 x B200 for 64 MB - 1 GB (profiles/sweep_8gpu.md)

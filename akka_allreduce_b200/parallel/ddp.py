@@ -1,0 +1,71 @@
+"""DDP communication hook backed by the fused allreduce kernel.
+
+Data-parallel gradient sync is the use the reference's primitive is meant for (source = gradients,
+sink = summed gradients, ``count`` lets the sink normalise partial sums: SURVEY.md 2.3); the
+reference has no training loop of its own.  Here every DDP gradient bucket becomes one allreduce
+round: the hook launches the kernel on a side stream as soon as the bucket is ready — so the
+transfer overlaps the rest of the backward pass — and returns a CUDA-aware future.  Gradients are
+averaged in the kernel's reduce phase (division by the contributor count), so with thresholds < 1 a
+straggler's missing contribution does not bias the mean.
+
+    model = DDP(model, device_ids=[local_rank])
+    hook = AllreduceCommHook(rank, world, local_rank)
+    model.register_comm_hook(None, hook)
+"""
+from typing import Dict, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .engine import DeviceAllreduce, default_uds_dir
+
+
+class AllreduceCommHook:
+    def __init__(self, rank: int, world: int, device: int, max_chunk_bytes: int = 1 << 20, max_lag: int = 1,
+                 th_reduce: float = 1.0, th_complete: float = 1.0, uds_dir: Optional[str] = None,
+                 timeout_ms: float = 30_000.0, algo: str = "auto", ctas: Optional[int] = None):
+        self.rank, self.world, self.device_index = rank, world, device
+        self.__name__ = self.__qualname__ = "akka_allreduce_b200_fused_allreduce_hook"  # DDP logs the hook's name
+        self.device = torch.device("cuda", device)
+        self.max_chunk_bytes, self.max_lag = max_chunk_bytes, max_lag
+        self.th_reduce, self.th_complete = th_reduce, th_complete
+        self.uds_dir = uds_dir or default_uds_dir("ddp")
+        self.timeout_ms, self.algo, self.ctas = timeout_ms, algo, ctas
+        self.stream = torch.cuda.Stream(device=self.device)
+        self._engines: Dict[Tuple[int, torch.dtype], DeviceAllreduce] = {}
+        self.buckets_reduced = 0
+        self.kernel_launches = 0
+
+    def _engine(self, numel: int, dtype: torch.dtype) -> DeviceAllreduce:
+        key = (numel, dtype)
+        eng = self._engines.get(key)
+        if eng is None:
+            # Every rank meets the same bucket sizes in the same order, so engines (and their symmetric
+            # regions) are created collectively on first use.  Blocks are aligned so that any bucket
+            # length runs on the 16-byte paths.
+            esz = torch.empty((), dtype=dtype).element_size()
+            eng = DeviceAllreduce(self.rank, self.world, numel, max(1, self.max_chunk_bytes // esz), self.max_lag,
+                                  dtype=dtype, th_reduce=self.th_reduce, th_complete=self.th_complete,
+                                  device=self.device_index, uds_dir=self.uds_dir, align_blocks=True,
+                                  timeout_ms=self.timeout_ms, normalize=True, algo=self.algo, ctas=self.ctas)
+            self._engines[key] = eng
+        return eng
+
+    def __call__(self, state, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+        buf = bucket.buffer()
+        eng = self._engine(buf.numel(), buf.dtype)
+        fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[self.device])
+        self.stream.wait_stream(torch.cuda.current_stream(self.device))  # the bucket's gradients are final
+        with torch.cuda.stream(self.stream):
+            before = eng.launcher.launches
+            eng.allreduce(buf, buf, None, stream=self.stream)  # in place: mean over the contributors
+            self.kernel_launches += eng.launcher.launches - before
+            buf.record_stream(self.stream)
+            fut.set_result(buf)  # captures the side stream's position
+        self.buckets_reduced += 1
+        return fut
+
+    def close(self) -> None:
+        for eng in self._engines.values():
+            eng.close()
+        self._engines.clear()

@@ -139,9 +139,15 @@ class DeviceWorker:
                       "symmetric region %.1f MiB, multicast %s", self.id, self.device_index, world, init.th_reduce,
                       init.th_complete, init.max_lag, eng.launcher.sym_bytes / 2 ** 20, eng.has_multicast)
         stream = torch.cuda.Stream(device=dev)
-        outs = [torch.empty(n, dtype=dtype, device=dev) for _ in range(L)]
+        copy_stream = torch.cuda.Stream(device=dev)  # H2D of round r+1 overlaps the kernel of round r
+        staged = [torch.cuda.Event() for _ in range(L)]
+        # Sink: the round's symmetric sink slot itself when the layout allows (valid until the slot is
+        # recycled maxLag+1 rounds later), else a private ring of L output buffers.
+        outs = [eng.output_view(k) if eng.output_view(k) is not None else torch.empty(n, dtype=dtype, device=dev)
+                for k in range(L)]
         counts = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(L)]
-        stage = [None] * L
+        # Staging for host inputs: the symmetric staging slot when the kernel can read it in place (NVLS).
+        stage = [eng.input_view(k) for k in range(L)]
         events = [torch.cuda.Event() for _ in range(L)]
         inflight: list[int] = []
 
@@ -178,14 +184,18 @@ class DeviceWorker:
                 data = torch.as_tensor(data)
             if data.numel() != n:
                 raise ValueError(f"Input data size {data.numel()} is different from initialization time {n}!")
-            with torch.cuda.stream(stream):
-                if data.device != dev or data.dtype != dtype:
-                    if stage[slot] is None:
-                        stage[slot] = torch.empty(n, dtype=dtype, device=dev)
+            if data.device != dev or data.dtype != dtype:
+                if stage[slot] is None:
+                    stage[slot] = torch.empty(n, dtype=dtype, device=dev)
+                with torch.cuda.stream(copy_stream):
+                    # the slot was last read by round r-L, which has been flushed (its event synchronised)
                     stage[slot].copy_(data, non_blocking=True)  # H2D from (ideally pinned) host memory
-                    if data.device.type == "cpu":
-                        self.h2d_bytes += data.numel() * data.element_size()
-                    data = stage[slot]
+                    staged[slot].record(copy_stream)
+                stream.wait_event(staged[slot])
+                if data.device.type == "cpu":
+                    self.h2d_bytes += data.numel() * data.element_size()
+                data = stage[slot]
+            with torch.cuda.stream(stream):
                 eng.allreduce(data, outs[slot], counts[slot], round_=r, stream=stream)
                 events[slot].record(stream)
             inflight.append(r)
