@@ -73,6 +73,8 @@ def lib() -> C.CDLL:
     l.aar_scratch_force_offset.argtypes = [i64, i64, i32, i64]
     l.aar_allreduce_round.restype = i32
     l.aar_allreduce_round.argtypes = [C.POINTER(AarLaunch), vp]
+    l.aar_allreduce_round_static_scratch.restype = i32
+    l.aar_allreduce_round_static_scratch.argtypes = [C.POINTER(AarLaunch), vp]
     l.aar_max_emu_ctas.restype = i32
     l.aar_max_emu_ctas.argtypes = [i32, i32]
     l.aar_heap_create.restype = i32

@@ -30,6 +30,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <mutex>
 #include <string>
 
 #include "aar/device_layout.h"
@@ -1142,6 +1143,67 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
   if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_algo<__nv_bfloat16, __nv_bfloat16>(kp, stream);
   if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_F32) return launch_algo<__nv_bfloat16, float>(kp, stream);
   return fail(AAR_EUNSUPPORTED, "dtype combination not supported (f32/f32, bf16/bf16, bf16/f32)");
+}
+
+// ---------------------------------------------------------------- entry point that allocates nothing
+// The scratch of aar_allreduce_round() is normally a buffer the caller allocated.  This variant keeps it
+// in the library image instead: a fixed array in device global memory, 16 KB per (emulated) rank, that
+// every GPU loading the library carries until the process exits.
+#define AAR_STATIC_SCRATCH_PER_RANK 16384
+#define AAR_STATIC_SCRATCH_MAX_DEVICES 64
+
+}  // extern "C"
+
+namespace aar {
+static __device__ __align__(256) unsigned char g_static_scratch[AAR_MAX_RANKS * AAR_STATIC_SCRATCH_PER_RANK];
+}
+
+extern "C" {
+
+int aar_allreduce_round_static_scratch(const AarLaunch* a, void* stream_v) {
+  if (a == nullptr) return fail(AAR_EINVAL, "null launch");
+  if (a->world < 1 || a->world > AAR_MAX_RANKS || a->n <= 0 || a->max_chunk <= 0)
+    return fail(AAR_EINVAL, "bad world/size arguments");
+  const int64_t need = aar_scratch_bytes(a->n, a->max_chunk, a->world, a->block_step);
+  if (need > AAR_STATIC_SCRATCH_PER_RANK)
+    return fail(AAR_ETOOBIG, "this configuration needs " + std::to_string(need) +
+                                 " bytes of scratch per rank, the built-in scratch holds " +
+                                 std::to_string(AAR_STATIC_SCRATCH_PER_RANK) +
+                                 ": use fewer chunks per block (a larger maxChunkSize) or aar_allreduce_round() "
+                                 "with a scratch buffer of your own");
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+  if (dev < 0 || dev >= AAR_STATIC_SCRATCH_MAX_DEVICES) return fail(AAR_EUNSUPPORTED, "device ordinal beyond 63");
+
+  // Set-up, once per device, with that device current: in host code the array's name is only a stand-in,
+  // the address a kernel can use comes from cudaGetSymbolAddress().
+  static std::mutex mu;
+  static unsigned char* base_of[AAR_STATIC_SCRATCH_MAX_DEVICES] = {};
+  unsigned char* base = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(mu);
+    if (base_of[dev] == nullptr) {
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_static_scratch);
+      if (e != cudaSuccess || p == nullptr)
+        return fail(AAR_ECUDA, std::string("cudaGetSymbolAddress(built-in scratch): ") + cudaGetErrorString(e));
+      base_of[dev] = static_cast<unsigned char*>(p);
+    }
+    base = base_of[dev];
+  }
+
+  AarLaunch with_scratch = *a;
+  const int ranks_here = a->emu ? a->world : 1;
+  for (int r = 0; r < AAR_MAX_RANKS; ++r)
+    with_scratch.scratch[r] = r < ranks_here ? base + static_cast<size_t>(r) * AAR_STATIC_SCRATCH_PER_RANK : nullptr;
+  // The array still holds whatever the previous call left (counters of a round that timed out, another
+  // geometry's layout, a force tag): everything the kernel expects to find zero is cleared first, on the
+  // caller's stream so the order with earlier launches on that stream is kept.
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  e = cudaMemsetAsync(base, 0, static_cast<size_t>(ranks_here) * AAR_STATIC_SCRATCH_PER_RANK, stream);
+  if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("clearing the built-in scratch: ") + cudaGetErrorString(e));
+  return aar_allreduce_round(&with_scratch, stream_v);
 }
 
 }  // extern "C"

@@ -83,6 +83,29 @@ int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_
  * (>0) or a negative error. */
 int aar_allreduce_round(const AarLaunch* launch, void* stream);
 
+/* Same round as aar_allreduce_round(), for callers that cannot allocate device memory.  (No counterpart
+ * in the reference: it has no device memory to manage.)
+ *
+ * Who that is: a process that handed the whole GPU to its own memory pool when it started (an
+ * inference server that reserves HBM up front leaves nothing for a later cudaMalloc); a control loop
+ * that must not stall (cudaMalloc synchronises the device); a host that embeds this library through
+ * the C ABI alone and has no allocator of its own to give it buffers.  For them the kernel's scratch —
+ * the tile counters and per-chunk decisions that aar_allreduce_round() takes from launch->scratch[] —
+ * lives in the library image: a fixed array of 16 KB per rank (16 ranks: 256 KB) in the global memory
+ * of every GPU that loads the library, held until the process exits.  launch->scratch[] is ignored;
+ * inputs, outputs and the symmetric region are still the caller's.
+ *
+ * - Limit: aar_scratch_bytes() of the configuration must be <= 16384 (roughly world x chunks-per-block
+ *   <= 3000); beyond that the call fails with AAR_ETOOBIG and a message naming both numbers.
+ * - It calls no cudaMalloc/cudaFree and no allocating library routine; the array is cleared with a
+ *   cudaMemsetAsync on `stream` before each launch, so nothing carries over from the previous call
+ *   (this also means the host-side force tag is always 0 here: rounds close by threshold or timeout).
+ * - The first call on each device looks the array's device address up (that device must be current);
+ *   make that first call before you start capturing any stream.
+ * - All calls in the process share the one array per device.  Two rounds that overlap on the GPU
+ *   (different streams, or two engines) would corrupt each other's counters: serialise them. */
+int aar_allreduce_round_static_scratch(const AarLaunch* launch, void* stream);
+
 /* Co-residency limit for emulation mode: max work CTAs per rank so that world*(ctas+1) blocks fit. */
 int aar_max_emu_ctas(int world, int device);
 
