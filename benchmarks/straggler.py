@@ -1,0 +1,161 @@
+#!/usr/bin/env python
+"""Rounds/sec and correctness under thresholds < 1 with injected stragglers (BASELINE.json config 3).
+
+    python benchmarks/straggler.py --emulate 8                 # one GPU: in-kernel delays/mutes, correctness
+    torchrun --nproc-per-node 8 benchmarks/straggler.py        # real ranks: AllreduceMaster + DeviceWorker,
+                                                               # straggler ranks sleep in their data source
+
+Config: thReduce = thComplete = 0.75, online-nodes threshold thAllreduce = 0.75 (6 of 8), maxLag = 4.
+Every rank's message is the constant 2^rank, so a reduced value IS the bitmask of its contributors:
+for every element the number of set bits must equal the reported count (partial sums numerically
+correct against `count`), and a count of 0 must come with a value of 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import random
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import torch
+
+
+def check(data: torch.Tensor, count: torch.Tensor) -> bool:
+    bits = data.to(torch.int64)
+    pop = torch.zeros_like(bits)
+    for b in range(16):
+        pop += (bits >> b) & 1
+    return bool((pop == count.to(torch.int64)).all()) and bool((data == bits.to(data.dtype)).all())
+
+
+def emulated(args) -> dict:
+    from akka_allreduce_b200.ops.fused_allreduce import EmulatedCluster, Injection
+
+    P, n, mc = args.emulate, args.size, args.chunk
+    cl = EmulatedCluster(P, n, mc, max_lag=4, th_reduce=0.75, th_complete=0.75, th_allreduce=0.75, timeout_ms=args.timeout_ms)
+    srcs = [torch.full((n,), float(1 << r), device="cuda") for r in range(P)]
+    rng = random.Random(0)
+    ok, hist = True, {}
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for r in range(args.rounds):
+        late = rng.sample(range(P), rng.choice([0, 1, 2]))
+        inj = Injection(delay_ns={k: args.delay_us * 1000 for k in late[:1]}, mute=sum(1 << k for k in late[1:]))
+        outs, counts = cl.run_round(srcs, inj)
+        if r % 10 == 0 or late:
+            torch.cuda.synchronize()
+            for i in range(P):
+                ok = ok and check(outs[i], counts[i])
+            for c in counts[0].unique().tolist():
+                hist[c] = hist.get(c, 0) + 1
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    return {"mode": "emulated", "workers": P, "bytes": n * 4, "rounds": args.rounds, "rounds_per_s": round(args.rounds / dt, 1),
+            "partial_sums_match_counts": ok, "count_values_seen_on_rank0": {str(k): v for k, v in sorted(hist.items())},
+            "timeouts": cl.timeouts_seen()}
+
+
+def distributed(args) -> dict:
+    import torch.distributed as dist
+
+    from akka_allreduce_b200 import AllReduceInput, AllreduceConfig
+    from akka_allreduce_b200.master import AllreduceMaster
+    from akka_allreduce_b200.parallel.device_worker import DeviceWorker
+
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    cfg = AllreduceConfig()
+    cfg.worker.totalSize, cfg.worker.maxLag = world, 4
+    cfg.data.dataSize, cfg.data.maxChunkSize, cfg.data.maxRound = args.size, args.chunk, args.rounds - 1
+    cfg.thresholds.thAllreduce = cfg.thresholds.thReduce = cfg.thresholds.thComplete = 0.75
+    cfg.device.backend, cfg.device.gate, cfg.device.timeoutMs = "cuda", "device", args.timeout_ms
+    cfg.cluster.port = int(os.environ["MASTER_PORT"]) + 59
+    master = AllreduceMaster(cfg) if rank == 0 else None
+    if master:
+        master.start()
+    stragglers = set(range(world - args.stragglers, world))      # the last k ranks are slow
+    rng = random.Random(rank)
+    state = {"ok": True, "done": 0, "min_count": 99, "zero_elems": 0, "t0": None, "t1": None}
+    mine = None
+
+    def source(req):
+        nonlocal mine
+        if mine is None:
+            mine = torch.full((args.size,), float(1 << state["id"]), device=dev)
+        if rank in stragglers and rng.random() < args.straggle_prob:
+            time.sleep(args.delay_us * 1e-6)                     # a slow data source = a straggling worker
+        return AllReduceInput(mine)
+
+    def sink(out):
+        if state["t0"] is None:
+            state["t0"] = time.perf_counter()
+        state["t1"] = time.perf_counter()
+        state["done"] += 1
+        if out.iteration % args.check_every == 0:
+            state["ok"] = state["ok"] and check(out.data, out.count)
+            state["min_count"] = min(state["min_count"], int(out.count.min()))
+            state["zero_elems"] += int((out.count == 0).sum())
+
+    w = DeviceWorker(source, sink, cfg, master_port=cfg.cluster.port, device=local)
+    orig = w._run
+
+    def run_with_id():
+        # the worker id (= bit of this rank's contribution) is only known after InitWorkers
+        while w._init is None and not w._stop:
+            time.sleep(0.001)
+        state["id"] = w._init.dest_id if w._init is not None else 0
+        orig()
+
+    w._run = run_with_id
+    dist.barrier()
+    w.start()
+    finished = w.wait(600)
+    w.stop()
+    if master:
+        master.wait(30)
+        master.stop()
+    secs = (state["t1"] - state["t0"]) if state["t0"] else float("nan")
+    t = torch.tensor([float(state["ok"]), state["done"], secs, state["min_count"], state["zero_elems"]],
+                     dtype=torch.float64, device=dev)
+    allt = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(allt, t)
+    dist.barrier()
+    dist.destroy_process_group()
+    rows = [x.tolist() for x in allt]
+    fast = [r for i, r in enumerate(rows) if i not in stragglers]
+    return {"mode": "distributed", "workers": world, "straggler_ranks": sorted(stragglers), "bytes": args.size * 4,
+            "rounds": args.rounds, "finished": bool(finished),
+            "rounds_per_s_fast_ranks": round(min(r[1] / r[2] for r in fast), 1),
+            "rounds_per_s_slowest_rank": round(min(r[1] / r[2] for r in rows), 1),
+            "partial_sums_match_counts": all(r[0] == 1.0 for r in rows),
+            "min_count_seen": int(min(r[3] for r in rows)), "elements_with_count_0": int(sum(r[4] for r in rows)),
+            "thresholds": "thReduce=thComplete=0.75, thAllreduce=0.75, maxLag=4", "delay_us": args.delay_us,
+            "straggle_prob": args.straggle_prob}
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--emulate", type=int, default=0)
+    ap.add_argument("--size", type=int, default=1 << 22)       # 16 MB fp32
+    ap.add_argument("--chunk", type=int, default=1 << 16)      # 256 KB chunks
+    ap.add_argument("--rounds", type=int, default=300)
+    ap.add_argument("--stragglers", type=int, default=2)
+    ap.add_argument("--straggle-prob", type=float, default=0.3)
+    ap.add_argument("--delay-us", type=int, default=2000)
+    ap.add_argument("--timeout-ms", type=float, default=50.0)
+    ap.add_argument("--check-every", type=int, default=5)
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    res = emulated(a) if a.emulate else distributed(a)
+    if int(os.environ.get("RANK", "0")) == 0:
+        print(json.dumps(res), flush=True)
+        if a.out:
+            with open(a.out, "w") as f:
+                f.write(json.dumps(res) + "\n")
+    sys.exit(0 if res["partial_sums_match_counts"] else 1)
