@@ -67,6 +67,7 @@ class RoundLauncher:
         a.fast_fences = 1 if os.environ.get("AAR_FAST_FENCES") else 0
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
+        a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate

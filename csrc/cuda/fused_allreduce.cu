@@ -198,11 +198,10 @@ __device__ __forceinline__ void reduce_tile(const TW* const* __restrict__ rows, 
 // NVLS form of the same tile: one multimem.ld_reduce pulls the switch-reduced sum of every rank's
 // staging slot, one multimem.st lands the result in every rank's sink slot.  Only used when all P
 // contributions are present (an in-switch reduction cannot leave a peer out).
-template <typename TW>
-__device__ __forceinline__ void nvls_reduce_tile(const TW* __restrict__ mc_src, TW* __restrict__ mc_dst, int len,
+template <typename TW, int B>
+__device__ __noinline__ void nvls_reduce_tile(const TW* __restrict__ mc_src, TW* __restrict__ mc_dst, int len,
                                                  float post) {
   constexpr int E = 16 / sizeof(TW);
-  constexpr int B = 8;
   using U = Unit<TW, E>;
   const int units = len / E;
   const uint4* s = reinterpret_cast<const uint4*>(mc_src);
@@ -687,7 +686,11 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       if (kNvls && mask == all_ranks && dest_ok == all_ranks && vec && len % EW == 0) {
         const int64_t so = p.sym.off_scat + (p.sym.scat_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
         const int64_t to = p.sym.off_sink + (p.sym.sink_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
-        nvls_reduce_tile<TW>(reinterpret_cast<const TW*>(p.a.mc_base + so), reinterpret_cast<TW*>(p.a.mc_base + to), len, post);
+        // 8 switch requests in flight per thread; nvls_unroll = 16 doubles that (spills a little: experiments)
+        if (p.a.nvls_unroll == 16)
+          nvls_reduce_tile<TW, 16>(reinterpret_cast<const TW*>(p.a.mc_base + so), reinterpret_cast<TW*>(p.a.mc_base + to), len, post);
+        else
+          nvls_reduce_tile<TW, 8>(reinterpret_cast<const TW*>(p.a.mc_base + so), reinterpret_cast<TW*>(p.a.mc_base + to), len, post);
       } else {
         reduce_tile<TW>(sh_rows, mask, P, sh_dst, P, len, post, vec);
       }
