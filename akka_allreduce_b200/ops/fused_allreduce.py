@@ -47,6 +47,14 @@ class RoundLauncher:
         self.req_reduce = geo.req_reduce(th_reduce)
         self.req_complete = geo.req_complete(th_complete)
         self.gate = 0 if th_allreduce is None else gate_count(th_allreduce, geo.world)
+        # With every threshold at 1 a rank cannot finish round r without everybody's contribution to r, so
+        # nobody can be more than one round ahead and the thAllreduce gate is implied by the data flow itself:
+        # with at least two ring slots the in-kernel wait on the peers' completion flags is skipped.
+        if (self.gate >= geo.world and self.req_reduce >= geo.world and self.req_complete >= geo.total_chunks
+                and geo.slots >= 2 and os.environ.get("AAR_KEEP_GATE") is None):
+            self.gate_implied, self.gate = True, 0
+        else:
+            self.gate_implied = False
         self.sym_bytes = self.lib.aar_sym_bytes(geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code, os_cap,
                                                 geo.block_step_arg)
         self.flag_bytes = self.lib.aar_sym_flag_bytes(geo.n, geo.max_chunk, geo.world, geo.slots, self.wire_code,
@@ -68,6 +76,7 @@ class RoundLauncher:
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))
+        a.part_kb = int(os.environ.get("AAR_PART_KB", 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate

@@ -1107,8 +1107,15 @@ int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
     kp.n_c = a->role_c;
     kp.n_r = a->ctas - kp.n_s - kp.n_c;
   }
+  // Work items: a chunk is cut into equal parts (multiples of one full CTA sweep) so that each phase has at
+  // least two items per CTA, and no part is larger than `part_kb` (default 256 KB): all CTAs of a phase then
+  // walk through memory inside a window of ctas x part, which keeps the pages they touch at any one time
+  // within TLB reach even for GB-sized messages.
+  const int64_t cap_elems = (static_cast<int64_t>(a->part_kb > 0 ? a->part_kb : 256) << 10) / wb;
   auto split = [&](int64_t items_without_split, int ctas_of_role, int& part, int& tpc) {
     int64_t want = ceil_div(2 * static_cast<int64_t>(ctas_of_role), items_without_split > 0 ? items_without_split : 1);
+    const int64_t for_cap = ceil_div(chunk_len, cap_elems > sweep ? cap_elems : sweep);
+    if (want < for_cap) want = for_cap;
     const int64_t most = ceil_div(chunk_len, sweep);
     if (want > most) want = most;
     if (want < 1) want = 1;
