@@ -76,7 +76,10 @@ class RoundLauncher:
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))
-        a.part_kb = int(os.environ.get("AAR_PART_KB", 0))
+        # largest work item: 256 KB, 64 KB for messages of 512 MB and more (measured on 8 GPUs at 1 GB: 64 KB
+        # 2.93 ms, 256 KB 3.01 ms, 1 MB 3.11 ms — smaller windows keep the pages in flight within TLB reach)
+        big = g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20)
+        a.part_kb = int(os.environ.get("AAR_PART_KB", 64 if big else 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate

@@ -63,7 +63,8 @@ class DeviceAllreduce:
         # One-shot (every rank sums all P copies itself) is the latency path for small messages; it needs
         # thresholds of 1 (ranks reduce independently, so they must all see the same contributors).
         oneshot_ok = oneshot_eligible(self.geo, th_reduce, th_complete, max_lag, th_allreduce)
-        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", 256 << 10))
+        # crossover measured on B200s (profiles/sweep_*): one hop wins up to 1 MB on 2-4 GPUs, 512 KB on 8
+        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", (1 << 20) if world <= 4 else (512 << 10)))
         if algo == "oneshot" and not oneshot_ok:
             raise K.AarError("algo=oneshot needs thReduce = thComplete = 1 and maxLag >= 1 (or the thAllreduce gate)")
         use_oneshot = algo == "oneshot" or (algo == "auto" and oneshot_ok and small and world > 1)
@@ -81,7 +82,10 @@ class DeviceAllreduce:
         self.mc_ptr = mc.value  # None when the driver exposes no multicast
         # NVLS reduces inside the switch over ALL ranks, so it is only eligible when no contribution may be
         # left out (thReduce = 1); chunks that time out fall back to unicast pulls inside the same kernel.
-        nvls_ok = bool(self.mc_ptr) and world > 2 and self.launcher.req_reduce >= world  # at 2 ranks push moves the same bytes
+        # NVLS moves N + N/P bytes per direction against 2N(P-1)/P for push: nothing to gain at 2 ranks, and at
+        # 3-4 ranks the push kernel was measured faster from 16 MB up (profiles/sweep_4gpu_*).
+        nvls_ok = bool(self.mc_ptr) and self.launcher.req_reduce >= world and (
+            world >= 5 or (world >= 3 and n * elem < (16 << 20)))
         if algo == "nvls" and not (bool(self.mc_ptr) and world > 1 and self.launcher.req_reduce >= world):
             raise K.AarError("algo=nvls needs a multicast alias (NVLS), world > 1 and thReduce = 1")
         if use_oneshot:
