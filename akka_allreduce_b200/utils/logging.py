@@ -10,7 +10,7 @@ _FMT = "[%(levelname)s] [%(asctime)s] [%(name)s] %(message)s"
 def get_logger(name: str, level: str = "INFO") -> logging.Logger:
     log = logging.getLogger("aar." + name)
     if not log.handlers:
-        h = logging.StreamHandler(sys.stdout)
+        h = logging.StreamHandler(sys.stderr)  # stdout is for results (bench JSON line, throughput prints)
         h.setFormatter(logging.Formatter(_FMT))
         log.addHandler(h)
         log.propagate = False

@@ -229,3 +229,31 @@ def test_oneshot_timeout_leaves_out_the_silent_rank():
     want = _ref_sum(srcs, ranks=[0, 2, 3])
     for i in range(world):
         assert torch.equal(outs[i], want) and bool((counts[i] == 3).all())
+
+
+def test_cli_worker_cuda_backend_single_gpu():
+    """`python -m akka_allreduce_b200.worker --backend cuda` against a CLI master: the reference's launcher
+    pair (README.md:3,7) on the CUDA backend, with the built-in ramp source and throughput/assert sink."""
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, PYTHONPATH=root)
+    port = 28000 + os.getpid() % 1500
+    m = subprocess.Popen([sys.executable, "-m", "akka_allreduce_b200.master", str(port), "1", "4096", "512",
+                          "--maxRound", "60", "--thComplete", "1.0"], env=env, stdout=subprocess.PIPE,
+                         stderr=subprocess.STDOUT, text=True)
+    w = subprocess.Popen([sys.executable, "-m", "akka_allreduce_b200.worker", "0", "4096", "--master-port", str(port),
+                          "--checkpoint", "20", "--assert-multiple", "1", "--backend", "cuda"], env=env,
+                         stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    try:
+        wout = w.communicate(timeout=120)[0]
+        mout = m.communicate(timeout=30)[0]
+    finally:
+        for p in (w, m):
+            if p.poll() is None:
+                p.kill()
+    assert w.returncode == 0, wout[-2000:]
+    assert m.returncode == 0, mout[-2000:]
+    assert "MBytes/sec" in wout and "----Data output at #40" in wout
