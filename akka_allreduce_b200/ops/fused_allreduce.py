@@ -73,6 +73,8 @@ class RoundLauncher:
         a.in_dtype, a.wire_dtype = self.in_code, self.wire_code
         a.ctas, a.use_tma = self.ctas, 0 if os.environ.get("AAR_NO_TMA") else 1
         a.fast_fences = 1 if os.environ.get("AAR_FAST_FENCES") else 0
+        # interleaving completion items with reduce items: measured neutral-to-slower (2 GPUs), off by default
+        a.overlap_flush = 1 if os.environ.get("AAR_OVERLAP") else 0
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))

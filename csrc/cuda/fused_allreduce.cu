@@ -630,6 +630,102 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   }
   if (trace != nullptr && threadIdx.x == 0) trace[2] = globaltimer_ns();
 
+  // ---- phase C as a re-entrant step: assemble output + counts as reduced chunks are acknowledged ----
+  // `complete_step(false)` handles this CTA's next completion item only if its chunk has already been
+  // acknowledged, `complete_step(true)` waits for it.  The reduce loop below calls the non-blocking form after
+  // every item, so the HBM-bound flush of chunks that peers have already delivered overlaps the NVLink-bound
+  // reduce+broadcast instead of running as a tail after it.
+  const uint32_t* cw = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_complete);
+  const uint32_t* bitmap = cw + 4;
+  const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + p.sym.arr_index(c.slot, 0, 0);
+  const bool c_pure_copy = tma && sizeof(TIn) == sizeof(TW);
+  const int c_tile = p.part_c, c_tpc = p.tpc_c;
+  const int c_items = do_c ? cpb * P * c_tpc : 0;
+  int c_item = c_idx;
+  auto complete_step = [&](bool blocking) -> bool {
+    int k = 0, o = 0, ch = 0, ntiles = 0;
+    int64_t bsize = 0, cb = 0, ce = 0;
+    for (; c_item < c_items; c_item += c_stride) {  // skip slots of the item grid that hold no data
+      k = c_item % c_tpc;
+      o = ((c_item / c_tpc) % P + c.rank) % P;
+      ch = c_item / (c_tpc * P);
+      bsize = p.part.size(o);
+      if (ch >= num_chunks(bsize, p.a.max_chunk)) continue;
+      cb = chunk_begin(ch, p.a.max_chunk, bsize);
+      ce = chunk_end(ch, p.a.max_chunk, bsize);
+      ntiles = static_cast<int>(ceil_div(ce - cb, c_tile));
+      if (k < ntiles) break;
+    }
+    if (c_item >= c_items) return false;
+    const int64_t off = cb + static_cast<int64_t>(k) * c_tile;
+    const int len = static_cast<int>(min(static_cast<int64_t>(c_tile), ce - off));
+    const int idx = o * cpb + ch;
+    if (threadIdx.x == 0) {
+      const uint64_t w0 = trace != nullptr ? globaltimer_ns() : 0;
+      uint32_t state = 0;  // 0 not acknowledged yet, 1 present, 2 closed without it
+      for (;;) {
+        if ((ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u) {
+          state = 1;
+          break;
+        }
+        if (ld_volatile(cw) & kDecided) {  // closed: the snapshot is final
+          state = ((ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u) ? 1 : 2;
+          break;
+        }
+        if (!blocking) break;
+        if (globaltimer_ns() > c.deadline + 2 * p.a.timeout_ns + 1000000000ull) {  // the control CTA never answered
+          note_timeout(c);
+          state = 2;
+          break;
+        }
+        __nanosleep(64);
+      }
+      int cnt = 0;
+      if (state == 1) {
+        cnt = static_cast<int>(static_cast<uint32_t>(ld_volatile64(rflag + idx)));
+        __threadfence();
+      }
+      sh_word = state;
+      sh_cnt = cnt;
+      if (trace != nullptr && blocking) wait_c += globaltimer_ns() - w0;
+    }
+    __syncthreads();
+    const uint32_t state = sh_word;
+    const int cnt = sh_cnt;
+    __syncthreads();  // sh_word / sh_cnt are reused by the reduce loop
+    if (state == 0) return false;
+    const bool present = state == 1;
+    const TW* sink = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, o) + off;
+    const int64_t g = p.part.start(o) + off;
+    if (present && reinterpret_cast<const void*>(sink) == reinterpret_cast<const void*>(out + g)) {
+      // zero-copy sink: `out` IS this round's sink slot; only the contributor counts are left to write
+      if (counts != nullptr) {
+        int4* cp = reinterpret_cast<int4*>(counts + g);
+        const bool c16 = (reinterpret_cast<uintptr_t>(counts + g) & 15u) == 0;
+        const int quads = c16 ? len / 4 : 0;
+        for (int i = threadIdx.x; i < quads; i += kThreads) cp[i] = make_int4(cnt, cnt, cnt, cnt);
+        for (int i = quads * 4 + threadIdx.x; i < len; i += kThreads) counts[g + i] = cnt;
+      }
+    } else if (c_pure_copy && present && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
+      if (counts != nullptr && sh_tile_cnt != cnt) {  // (re)fill the shared tile of counts
+        int4* ct = reinterpret_cast<int4*>(ring.cnt_tile);
+        for (int i = threadIdx.x; i < kStageBytes / 16; i += kThreads) ct[i] = make_int4(cnt, cnt, cnt, cnt);
+        fence_proxy_async_smem();
+        __syncthreads();
+        if (threadIdx.x == 0) sh_tile_cnt = cnt;
+      }
+      if (threadIdx.x == 0)
+        tma_copy(ring, reinterpret_cast<uint8_t*>(out + g), reinterpret_cast<const uint8_t*>(sink),
+                 static_cast<int64_t>(len) * sizeof(TW), counts != nullptr ? reinterpret_cast<uint8_t*>(counts + g) : nullptr,
+                 sizeof(TW));
+    } else {
+      flush_tile<TW, TIn>(sink, out + g, counts != nullptr ? counts + g : nullptr, len, present, cnt, vec);
+    }
+    __syncthreads();
+    c_item += c_stride;
+    return true;
+  };
+
   // ---- phase R: reduce my block chunk by chunk and broadcast ----
   {
     const int64_t bsize = p.part.size(c.rank);
@@ -699,6 +795,10 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
         __threadfence();
         atomicAdd(red_cnt + ch, 1u);
       }
+      if (p.a.overlap_flush) {
+        while (complete_step(false)) {
+        }
+      }
     }
   }
   if (threadIdx.x == 0) {  // tells the publisher that this CTA will add nothing more to the S and R counters
@@ -707,84 +807,8 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   }
   if (trace != nullptr && threadIdx.x == 0) trace[3] = globaltimer_ns();
 
-  // ---- phase C: assemble output + counts as reduced chunks are acknowledged ----
-  {
-    const uint32_t* cw = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_complete);
-    const uint32_t* bitmap = cw + 4;
-    const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + p.sym.arr_index(c.slot, 0, 0);
-    const bool pure_copy = tma && sizeof(TIn) == sizeof(TW);
-    const int tile = p.part_c, tpc = p.tpc_c;
-    const int items = do_c ? cpb * P * tpc : 0;
-    for (int item = c_idx; item < items; item += c_stride) {
-      const int k = item % tpc;
-      const int o = ((item / tpc) % P + c.rank) % P;
-      const int ch = item / (tpc * P);
-      const int64_t bsize = p.part.size(o);
-      if (ch >= num_chunks(bsize, p.a.max_chunk)) continue;
-      const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
-      const int ntiles = static_cast<int>(ceil_div(ce - cb, tile));
-      if (k >= ntiles) continue;
-      const int64_t off = cb + static_cast<int64_t>(k) * tile;
-      const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
-      const int idx = o * cpb + ch;
-      if (threadIdx.x == 0) {
-        const uint64_t w0 = trace != nullptr ? globaltimer_ns() : 0;
-        bool present = false;
-        for (;;) {
-          if ((ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u) {
-            present = true;
-            break;
-          }
-          if (ld_volatile(cw) & kDecided) {  // closed: the snapshot is final
-            present = (ld_volatile(bitmap + (idx >> 5)) >> (idx & 31)) & 1u;
-            break;
-          }
-          if (globaltimer_ns() > c.deadline + 2 * p.a.timeout_ns + 1000000000ull) {  // the control CTA never answered
-            note_timeout(c);
-            break;
-          }
-          __nanosleep(64);
-        }
-        int cnt = 0;
-        if (present) {
-          cnt = static_cast<int>(static_cast<uint32_t>(ld_volatile64(rflag + idx)));
-          __threadfence();
-        }
-        sh_word = present ? 1u : 0u;
-        sh_cnt = cnt;
-        if (trace != nullptr) wait_c += globaltimer_ns() - w0;
-      }
-      __syncthreads();
-      const bool present = sh_word != 0;
-      const int cnt = sh_cnt;
-      const TW* sink = reinterpret_cast<const TW*>(c.my_sym + p.sym.off_sink) + p.sym.sink_elem(c.slot, o) + off;
-      const int64_t g = p.part.start(o) + off;
-      if (present && reinterpret_cast<const void*>(sink) == reinterpret_cast<const void*>(out + g)) {
-        // zero-copy sink: `out` IS this round's sink slot; only the contributor counts are left to write
-        if (counts != nullptr) {
-          int4* cp = reinterpret_cast<int4*>(counts + g);
-          const bool c16 = (reinterpret_cast<uintptr_t>(counts + g) & 15u) == 0;
-          const int quads = c16 ? len / 4 : 0;
-          for (int i = threadIdx.x; i < quads; i += kThreads) cp[i] = make_int4(cnt, cnt, cnt, cnt);
-          for (int i = quads * 4 + threadIdx.x; i < len; i += kThreads) counts[g + i] = cnt;
-        }
-      } else if (pure_copy && present && (static_cast<int64_t>(len) * sizeof(TW)) % 16 == 0) {
-        if (counts != nullptr && sh_tile_cnt != cnt) {  // (re)fill the shared tile of counts
-          int4* ct = reinterpret_cast<int4*>(ring.cnt_tile);
-          for (int i = threadIdx.x; i < kStageBytes / 16; i += kThreads) ct[i] = make_int4(cnt, cnt, cnt, cnt);
-          fence_proxy_async_smem();
-          __syncthreads();
-          if (threadIdx.x == 0) sh_tile_cnt = cnt;
-        }
-        if (threadIdx.x == 0)
-          tma_copy(ring, reinterpret_cast<uint8_t*>(out + g), reinterpret_cast<const uint8_t*>(sink),
-                   static_cast<int64_t>(len) * sizeof(TW), counts != nullptr ? reinterpret_cast<uint8_t*>(counts + g) : nullptr,
-                   sizeof(TW));
-      } else {
-        flush_tile<TW, TIn>(sink, out + g, counts != nullptr ? counts + g : nullptr, len, present, cnt, vec);
-      }
-      __syncthreads();
-    }
+  // ---- phase C, rest: whatever completion items the reduce loop did not get to, now blocking ----
+  while (complete_step(true)) {
   }
   __syncthreads();
   if (threadIdx.x == 0) {
