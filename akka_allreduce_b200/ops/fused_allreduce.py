@@ -73,8 +73,11 @@ class RoundLauncher:
         a.in_dtype, a.wire_dtype = self.in_code, self.wire_code
         a.ctas, a.use_tma = self.ctas, 0 if os.environ.get("AAR_NO_TMA") else 1
         a.fast_fences = 1 if os.environ.get("AAR_FAST_FENCES") else 0
-        # interleaving completion items with reduce items: measured neutral-to-slower (2 GPUs), off by default
-        a.overlap_flush = 1 if os.environ.get("AAR_OVERLAP") else 0
+        # Interleaving completion items with reduce items (flush of delivered chunks between reduce items):
+        # measured on 8 GPUs 1 GB 2.70 ms vs 2.93 ms without, 256 MB 0.70 vs 0.68, 64 MB equal; neutral on 2 GPUs.
+        # On for messages of 512 MB and more.  AAR_OVERLAP=1/0 forces it.
+        ov = os.environ.get("AAR_OVERLAP")
+        a.overlap_flush = int(ov) if ov in ("0", "1") else (1 if g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20) else 0)
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))
