@@ -45,6 +45,10 @@ class AarLaunch(C.Structure):
     ]
 
 
+class AarError(RuntimeError):
+    pass
+
+
 _lib = None
 
 
@@ -87,12 +91,13 @@ def lib() -> C.CDLL:
     l.aar_heap_destroy.argtypes = [vp]
     l.aar_last_error.restype = C.c_char_p
     l.aar_last_error.argtypes = []
+    l.aar_abi_sizeof_launch.restype = i32
+    l.aar_abi_sizeof_launch.argtypes = []
+    if l.aar_abi_sizeof_launch() != C.sizeof(AarLaunch):  # a drifted mirror would corrupt every launch silently
+        raise AarError(f"AarLaunch mirror is {C.sizeof(AarLaunch)} bytes, the library's struct {l.aar_abi_sizeof_launch()}: "
+                       "ops/cuda.py and include/aar_b200.h are out of sync")
     _lib = l
     return l
-
-
-class AarError(RuntimeError):
-    pass
 
 
 def check(rc: int, what: str = "") -> int:

@@ -1091,6 +1091,8 @@ int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_
   return ScratchLayout::make(world, s.cpb).off_fin_cnt + 8;
 }
 
+int aar_abi_sizeof_launch(void) { return static_cast<int>(sizeof(AarLaunch)); }
+
 int aar_max_emu_ctas(int world, int device) {
   int sms = 0, per_sm = 0;
   cudaFuncSetAttribute(aar_twoshot_kernel<float, float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);

@@ -82,6 +82,9 @@ int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block
  * every wait immediately (device form of the catch-up path, AllreduceWorker.scala:100-106). */
 int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_t block_step);
 
+/* sizeof(AarLaunch) as this library was compiled: bindings compare it with their own mirror of the struct. */
+int aar_abi_sizeof_launch(void);
+
 /* Launches one round on `stream` (a cudaStream_t).  Returns the number of kernels launched
  * (>0) or a negative error. */
 int aar_allreduce_round(const AarLaunch* launch, void* stream);

@@ -1,0 +1,48 @@
+"""Checks of the CUDA library that need no GPU: it loads without a driver, its C struct matches the ctypes
+mirror, and the Python geometry mirror agrees with the C++ layout/threshold code."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from akka_allreduce_b200 import host
+from akka_allreduce_b200.ops import cuda as K
+from akka_allreduce_b200.ops.geometry import Geometry, gate_count, threshold_count
+
+
+def test_library_loads_without_gpu_and_struct_matches():
+    lib = K.lib()
+    assert lib.aar_abi_sizeof_launch() == C.sizeof(K.AarLaunch)
+
+
+@pytest.mark.parametrize("th,n", [(0.7, 10), (0.7, 9), (0.8, 6), (0.8, 4), (0.75, 8), (0.9, 2), (1.0, 8), (0.6, 2), (0.5, 4)])
+def test_threshold_mirror_matches_cpp(th, n):
+    assert threshold_count(th, n) == host.threshold_count(th, n)
+
+
+@pytest.mark.parametrize("total,th", [(8, 0.75), (8, 1.0), (4, 0.75), (2, 1.0), (3, 0.5), (8, 0.8)])
+def test_gate_count_is_first_count_that_passes_master_gate(total, th):
+    k = gate_count(th, total)
+    assert host.master_gate(k, total, th) and (k == 0 or not host.master_gate(k - 1, total, th))
+
+
+@pytest.mark.parametrize("n,mc,P,lag", [(10, 2, 2, 1), (778, 3, 4, 3), (9, 2, 4, 1), (1 << 24, 1 << 18, 8, 1), (100003, 4096, 5, 2)])
+def test_geometry_mirror_matches_cpp_partition(n, mc, P, lag):
+    g = Geometry.make(n, mc, P, lag)
+    part = host.Partition(n, P)
+    assert [g.size(i) for i in range(P)] == [part.size(i) for i in range(P)]
+    assert g.total_chunks == part.total_reduced_chunks(mc)
+    lib = K.lib()
+    # layout sizes are pure functions of the configuration: callable on the CPU
+    assert lib.aar_sym_bytes(n, mc, P, lag + 1, K.F32, 0, 0) > 2 * (lag + 1) * n * 4
+    assert lib.aar_sym_bytes(n, mc, P, lag + 1, K.BF16, 0, 0) <= lib.aar_sym_bytes(n, mc, P, lag + 1, K.F32, 0, 0)
+    assert 0 < lib.aar_scratch_force_offset(n, mc, P, 0) < lib.aar_scratch_bytes(n, mc, P, 0)
+    ranges = list(g.chunk_ranges())
+    assert len(ranges) == g.total_chunks and ranges[-1][3] == n and all(a < b for _, _, a, b in ranges)
+
+
+def test_static_scratch_limit_is_checked_before_any_cuda_call():
+    """The no-allocation entry point validates the configuration first, so the refusal needs no GPU."""
+    a = K.AarLaunch()
+    a.world, a.n, a.max_chunk, a.block_step, a.emu = 8, 1 << 20, 16, 0, 1
+    assert K.lib().aar_allreduce_round_static_scratch(C.byref(a), None) == -4
