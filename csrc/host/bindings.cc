@@ -77,7 +77,7 @@ PYBIND11_MODULE(_aar_host, m) {
   py::class_<InitWorkers>(m, "InitWorkers")
       .def(py::init([](std::map<int, Endpoint> workers, int worker_num, Endpoint master, int dest_id,
                        float th_reduce, float th_complete, int max_lag, int64_t data_size,
-                       int64_t max_chunk_size) {
+                       int64_t max_chunk_size, int start_round) {
              InitWorkers x;
              x.workers = std::move(workers);
              x.worker_num = worker_num;
@@ -88,11 +88,12 @@ PYBIND11_MODULE(_aar_host, m) {
              x.max_lag = max_lag;
              x.data_size = data_size;
              x.max_chunk_size = max_chunk_size;
+             x.start_round = start_round;
              return x;
            }),
            py::arg("workers"), py::arg("worker_num"), py::arg("master"), py::arg("dest_id"),
            py::arg("th_reduce"), py::arg("th_complete"), py::arg("max_lag"), py::arg("data_size"),
-           py::arg("max_chunk_size"))
+           py::arg("max_chunk_size"), py::arg("start_round") = 0)
       .def_readwrite("workers", &InitWorkers::workers)
       .def_readwrite("worker_num", &InitWorkers::worker_num)
       .def_readwrite("master", &InitWorkers::master)
@@ -102,6 +103,7 @@ PYBIND11_MODULE(_aar_host, m) {
       .def_readwrite("max_lag", &InitWorkers::max_lag)
       .def_readwrite("data_size", &InitWorkers::data_size)
       .def_readwrite("max_chunk_size", &InitWorkers::max_chunk_size)
+      .def_readwrite("start_round", &InitWorkers::start_round)
       .def("__repr__", [](const InitWorkers& x) { return describe(Message(x)); });
 
   py::class_<StartAllreduce>(m, "StartAllreduce")

@@ -10,17 +10,29 @@ MasterEngine::MasterEngine(Endpoint self, MasterConfig cfg, Mailer* mailer, bool
     : self_(self), cfg_(cfg), mailer_(mailer), verbose_(verbose) {}
 
 int MasterEngine::member_up(Endpoint worker) {
-  // Ids follow arrival order.  The reference uses workers.size, which collides with a
-  // live id after a removal; a monotonic counter is identical until the first removal
-  // and never reuses an id afterwards.
-  const int id = next_id_++;
+  // Ids follow arrival order.  The reference uses workers.size, which collides with a live id after a
+  // removal; here a newcomer takes the lowest id that is free (so a replacement inherits the block of the
+  // worker it replaces), which is the same thing until the first removal.
+  int id = 0;
+  while (workers_.count(id)) ++id;
+  if (id >= cfg_.total_workers && round_ != -1) id = next_id_ > id ? next_id_ : id;  // surplus worker: unused id
+  next_id_ = id + 1 > next_id_ ? id + 1 : next_id_;
   workers_[id] = worker;
-  if (static_cast<int>(workers_.size()) >= cfg_.total_workers && round_ == -1) {
-    if (verbose_)
-      std::printf("----%zu (out of %d) workers are up\n", workers_.size(), cfg_.total_workers);
-    init_workers();
-    round_ = 0;
-    start_allreduce();
+  if (round_ == -1) {
+    if (static_cast<int>(workers_.size()) >= cfg_.total_workers) {
+      if (verbose_)
+        std::printf("----%zu (out of %d) workers are up\n", workers_.size(), cfg_.total_workers);
+      init_workers(0);
+      round_ = 0;
+      start_allreduce();
+    }
+  } else if (id < cfg_.total_workers) {
+    // The job is already running (the reference never initialises such a node): everybody
+    // gets the refreshed peer map — existing workers only update their peers (AllreduceWorker.scala:87-89)
+    // — and the newcomer is initialised at the current round and told to start it.
+    if (verbose_) std::printf("----worker joined a running job as id %d at round %d\n", id, round_);
+    init_workers(round_);
+    mailer_->send(worker, StartAllreduce{round_});
   }
   return id;
 }
@@ -58,7 +70,7 @@ void MasterEngine::handle(const Message& m) {
   }
 }
 
-void MasterEngine::init_workers() {
+void MasterEngine::init_workers(int start_round) {
   for (const auto& [id, ep] : workers_) {
     InitWorkers init;
     init.workers = workers_;
@@ -70,6 +82,7 @@ void MasterEngine::init_workers() {
     init.max_lag = cfg_.max_lag;
     init.data_size = cfg_.data_size;
     init.max_chunk_size = cfg_.max_chunk_size;
+    init.start_round = start_round;
     mailer_->send(ep, std::move(init));
   }
 }

@@ -41,7 +41,7 @@ class MasterEngine {
   bool finished() const { return round_ >= cfg_.max_round && done_last_; }
 
  private:
-  void init_workers();
+  void init_workers(int start_round);
   void start_allreduce();
 
   Endpoint self_;

@@ -26,6 +26,9 @@ struct InitWorkers {
   int max_lag = 0;
   int64_t data_size = 0;
   int64_t max_chunk_size = 1024;
+  // Extension (not in the reference): first round a worker that joins a RUNNING job takes part in.
+  // 0 for the initial broadcast, so the normal start-up is message-for-message the reference's.
+  int start_round = 0;
 };
 
 struct StartAllreduce {

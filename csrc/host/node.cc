@@ -404,6 +404,7 @@ void MasterNode::send(Endpoint to, Message msg) {
       w.put<int32_t>(x.max_lag);
       w.put<int64_t>(x.data_size);
       w.put<int64_t>(x.max_chunk_size);
+      w.put<int32_t>(x.start_round);
       w.put<uint32_t>(static_cast<uint32_t>(x.workers.size()));
       for (const auto& [id, ep] : x.workers) {
         const PeerAddress& a = addr_of_conn_[static_cast<int>(ep - kConnBase)];
@@ -600,6 +601,7 @@ void WorkerNode::on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) {
       x.max_lag = r.get<int32_t>();
       x.data_size = r.get<int64_t>();
       x.max_chunk_size = r.get<int64_t>();
+      x.start_round = r.get<int32_t>();
       x.master = kMasterEp;
       const uint32_t peers = r.get<uint32_t>();
       const PeerAddress me{listen_host_, listen_port_};
@@ -608,6 +610,15 @@ void WorkerNode::on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) {
         PeerAddress a;
         a.port = r.get<int32_t>();
         a.host = r.str();
+        auto known = peer_addr_.find(id);
+        if (known == peer_addr_.end() || !(known->second == a)) {  // new or replaced peer: forget the old route
+          dead_peers_.erase(id);
+          auto pc = peer_conn_.find(id);
+          if (pc != peer_conn_.end()) {
+            close_conn(pc->second);
+            peer_conn_.erase(pc);
+          }
+        }
         peer_addr_[id] = a;
         x.workers[id] = (a == me) ? kSelfEp : kPeerBase + id;
       }

@@ -69,9 +69,11 @@ void WorkerEngine::on_init(const InitWorkers& m) {
   th_reduce_ = m.th_reduce;
   th_complete_ = m.th_complete;
   max_lag_ = m.max_lag;
-  round_ = 0;
-  max_round_ = -1;
-  max_scattered_ = -1;
+  // A replacement that joins a running job starts at the master's current round instead of replaying
+  // (and force-completing) the whole history; start_round is 0 in the reference's flow.
+  round_ = m.start_round;
+  max_round_ = m.start_round - 1;
+  max_scattered_ = m.start_round - 1;
   completed_.clear();
   data_size_ = m.data_size;
   max_chunk_ = m.max_chunk_size;

@@ -146,3 +146,47 @@ def test_cli_processes_default_plumbing_config():
     for w, o in zip(ws, outs):
         assert w.returncode == 0, o
         assert "MBytes/sec" in o and "----Data output at #50" in o
+
+
+def test_tcp_replacement_worker_rejoins():
+    """Same elastic path over real sockets: kill one of 4 workers, start a replacement process-side worker,
+    the master hands it the vacated id and every peer re-routes to its new address."""
+    P, n = 4, 16
+    cfg = _cluster(P, n, 2, 400, th=(0.75, 0.75, 0.75), max_lag=3)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    seen = {}
+
+    def make(i):
+        def source(req):
+            return AllReduceInput(np.ones(n, dtype=np.float32))
+
+        def sink(out, i=i):
+            c = np.array(out.count)
+            seen.setdefault(i, []).append((out.iteration, int(c[12:16].min())))   # block of worker id 3
+
+        w = AllreduceWorker(source, sink, master_port=port)
+        w.start()
+        return w
+
+    workers = [make(i) for i in range(P)]
+    try:
+        t0 = time.time()
+        while master.round < 20 and time.time() - t0 < 20:
+            time.sleep(0.005)
+        workers[3].stop()
+        t0 = time.time()
+        while master.alive != 3 and time.time() - t0 < 10:
+            time.sleep(0.01)
+        assert master.alive == 3
+        repl = make("replacement")
+        workers.append(repl)
+        assert master.wait(60), f"master stuck at round {master.round}"
+        assert master.alive == 4 and repl.id == 3
+    finally:
+        for w in workers[:3] + workers[4:]:
+            w.stop()
+        master.stop()
+    rounds = [r for r, _ in seen["replacement"]]
+    assert rounds and min(rounds) >= 20          # joined at the current round
+    assert any(c > 0 for r, c in seen[0] if r > min(rounds) + 5)   # block 3 is being reduced again

@@ -123,3 +123,53 @@ def test_cluster_thresholds_one_any_shape(P, n, mc):
     for o in outs:
         for it, (d, c) in o.items():
             assert (d == P * (np.arange(n, dtype=np.float32) + it)).all() and (c == P).all()
+
+
+def test_replacement_worker_joins_running_job():
+    """Elastic recovery beyond the reference (a node that joins after round 0 is never
+    initialised there).  A worker dies mid-run, thresholds of 0.75 keep rounds going with count 3; a
+    replacement registers, inherits the vacated id and block, is initialised AT the current round, and the
+    counts go back to 4."""
+    P, n, mc = 4, 16, 2
+    bus = h.LocalBus()
+    c = cfg(total_workers=P, th_allreduce=0.75, th_reduce=0.75, th_complete=0.75, max_lag=2, data_size=n,
+            max_round=200, max_chunk_size=mc)
+    ep, master = bus.add_master(c)
+    outs = [dict() for _ in range(P + 1)]
+    src = lambda it: np.ones(n, dtype=np.float32)
+    eps, workers = [], []
+    for i in range(P):
+        w_ep, w = bus.add_worker(src, lambda d, cnt, it, i=i: outs[i].__setitem__(it, (d.copy(), cnt.copy())))
+        eps.append(w_ep)
+        workers.append(w)
+        master.member_up(w_ep)
+    while master.round < 20:
+        bus.run(200)
+    # worker 3 dies: the master drops it; what others still send it becomes dead letters
+    master.terminated(eps[3])
+    dead = bus.add_probe()
+    bus.take(dead)
+    died_at = master.round
+    while master.round < died_at + 30:
+        bus.run(200)
+    mid = max(outs[0])
+    assert outs[0][mid][1].max() <= 4 and master.round >= died_at + 30
+    # a replacement shows up
+    new_ep, neww = bus.add_worker(src, lambda d, cnt, it: outs[P].__setitem__(it, (d.copy(), cnt.copy())))
+    joined_at = master.round
+    assert master.member_up(new_ep) == 3 and sorted(master.workers) == [0, 1, 2, 3]
+    bus.run()
+    assert master.finished and neww.id == 3
+    assert min(outs[P]) >= joined_at            # it started at the current round, not at 0
+    # While worker 3 was gone nobody reduced block 3 (elements 12..15): count 0 there on the survivors; once
+    # the replacement owns it, it is reduced and broadcast again.  (Counts stay at 3: thReduce 0.75 fires on
+    # the 3rd arrival and reports 3, AllreduceSpec "missed scatter".)
+    block3 = slice(12, 16)
+    gone = [r for r in outs[0] if died_at + 5 < r < joined_at - 3]
+    assert gone and all(outs[0][r][1][block3].max() == 0 for r in gone)
+    back = [r for r in outs[0] if r > joined_at + 5]
+    assert back and any(outs[0][r][1][block3].min() > 0 for r in back)
+    for r in back:
+        d, cnt = outs[0][r]
+        assert (d[cnt > 0] == cnt[cnt > 0]).all()   # sum of ones == contributors
+    assert not neww.errors
