@@ -61,6 +61,7 @@ class DeviceWorker:
         self.rounds_completed = 0
         self.h2d_bytes = 0
         self.finished = threading.Event()
+        self._nvtx = os.environ.get("AAR_NVTX") is not None  # NVTX ranges per round phase for timeline tools
 
     # ---- coordinator messages (IO thread) ---------------------------------------------------------
     def _on_message(self, msg) -> None:
@@ -161,7 +162,7 @@ class DeviceWorker:
             self.rounds_completed += 1
 
         last = cfg.data.maxRound
-        r = 0
+        r = init.start_round  # 0 unless the master initialised us into a running job
         while r <= last:
             with self._cv:
                 if self._stop:
@@ -178,7 +179,11 @@ class DeviceWorker:
             while len(inflight) >= L or (inflight and events[inflight[0] % L].query()):
                 flush_oldest()
             slot = r % L
+            if self._nvtx:
+                torch.cuda.nvtx.range_push(f"aar.round{r}.fetch")
             inp = self.source(AllReduceInputRequest(r))
+            if self._nvtx:
+                torch.cuda.nvtx.range_pop()
             data = inp.data if isinstance(inp, AllReduceInput) else inp
             if not isinstance(data, torch.Tensor):
                 data = torch.as_tensor(data)
@@ -196,8 +201,12 @@ class DeviceWorker:
                     self.h2d_bytes += data.numel() * data.element_size()
                 data = stage[slot]
             with torch.cuda.stream(stream):
+                if self._nvtx:
+                    torch.cuda.nvtx.range_push(f"aar.round{r}.launch")
                 eng.allreduce(data, outs[slot], counts[slot], round_=r, stream=stream)
                 events[slot].record(stream)
+                if self._nvtx:
+                    torch.cuda.nvtx.range_pop()
             inflight.append(r)
             r += 1
         while inflight:
@@ -222,6 +231,12 @@ def start_device_worker(config: AllreduceConfig, data_size: int, checkpoint: int
         mbytes = out.data.numel() * 4.0 * checkpoint / 1e6
         print(f"----Data output at #{out.iteration} - {elapsed} s")
         print("%2.1f Mbytes in %2.1f seconds at %4.3f MBytes/sec" % (mbytes, elapsed, mbytes / elapsed), flush=True)
+        world = config.worker.totalSize
+        if world > 1:  # bus bandwidth, nccl-tests convention: algbw x 2(P-1)/P
+            esz = out.data.element_size()
+            alg = out.data.numel() * esz * checkpoint / 1e9 / elapsed
+            print("     = %.2f GB/s algorithm bandwidth, %.2f GB/s bus bandwidth over %d workers"
+                  % (alg, alg * 2 * (world - 1) / world, world), flush=True)
         if assert_multiple > 0:
             ok = bool((out.data == state["ramp"] * assert_multiple).all()) and bool((out.count == assert_multiple).all())
             if not ok:
