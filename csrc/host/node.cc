@@ -220,7 +220,8 @@ void TcpNode::queue_frame(int conn_id, Frame kind, const std::vector<uint8_t>& p
     std::lock_guard<std::mutex> g(cmd_mu_);
     cmd_frames_.emplace_back(conn_id, std::move(f));
   }
-  wake();
+  // The IO thread drains the queue itself before it polls again: only other threads need to wake it.
+  if (std::this_thread::get_id() != io_thread_id_) wake();
 }
 
 void TcpNode::queue_local(Message m) {
@@ -228,7 +229,7 @@ void TcpNode::queue_local(Message m) {
     std::lock_guard<std::mutex> g(cmd_mu_);
     cmd_local_.push_back(std::move(m));
   }
-  wake();
+  if (std::this_thread::get_id() != io_thread_id_) wake();
 }
 
 void TcpNode::close_conn(int conn_id) {
@@ -298,6 +299,7 @@ void TcpNode::pump_writes(Conn& c) {
 }
 
 void TcpNode::io_loop() {
+  io_thread_id_ = std::this_thread::get_id();
   auto last_tick = Clock::now();
   std::vector<pollfd> fds;
   std::vector<int> ids;

@@ -98,6 +98,7 @@ class TcpNode : public Mailer {
   int listen_fd_ = -1;
   int wake_fd_ = -1;
   std::thread thread_;
+  std::thread::id io_thread_id_{};
   std::atomic<bool> running_{false}, stop_flag_{false};
   std::map<int, Conn> conns_;
   int next_conn_ = 1;

@@ -257,3 +257,42 @@ def test_cli_worker_cuda_backend_single_gpu():
     assert w.returncode == 0, wout[-2000:]
     assert m.returncode == 0, mout[-2000:]
     assert "MBytes/sec" in wout and "----Data output at #40" in wout
+
+
+def test_ddp_comm_hook_single_rank_matches_plain_backward():
+    """DDP + the fused-allreduce communication hook in a one-rank process group: the gradients DDP ends up
+    with must equal those of the same model without DDP (mean over one contributor = identity), and the hook
+    must actually have launched the kernel for every bucket."""
+    import os
+
+    import torch.distributed as dist
+    from torch.nn.parallel import DistributedDataParallel as DDP
+
+    from akka_allreduce_b200.models.gpt2 import GPT2, GPT2Config
+    from akka_allreduce_b200.parallel.ddp import AllreduceCommHook
+
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", str(29800 + os.getpid() % 100))
+    dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+    try:
+        torch.manual_seed(0)
+        cfg = GPT2Config.tiny()
+        ref = GPT2(cfg).cuda()
+        model = GPT2(cfg).cuda()
+        model.load_state_dict(ref.state_dict())
+        ddp = DDP(model, device_ids=[0], bucket_cap_mb=1)
+        hook = AllreduceCommHook(0, 1, 0)
+        ddp.register_comm_hook(None, hook)
+        x = torch.randint(0, cfg.vocab_size, (4, 33), device="cuda")
+        for _ in range(2):  # the second iteration runs on DDP's rebuilt buckets
+            ref.zero_grad()
+            ddp.zero_grad()
+            ref(x[:, :-1], x[:, 1:]).backward()
+            ddp(x[:, :-1], x[:, 1:]).backward()
+            torch.cuda.synchronize()
+            for a, b in zip(ref.parameters(), model.parameters()):
+                torch.testing.assert_close(b.grad, a.grad, rtol=1e-5, atol=1e-6)
+        assert hook.buckets_reduced >= 2 and hook.kernel_launches == hook.buckets_reduced
+        hook.close()
+    finally:
+        dist.destroy_process_group()
