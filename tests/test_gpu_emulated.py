@@ -296,3 +296,34 @@ def test_ddp_comm_hook_single_rank_matches_plain_backward():
         hook.close()
     finally:
         dist.destroy_process_group()
+
+
+def test_random_straggler_stress_counts_always_explain_the_sums():
+    """Stress version of the partial-completion checks (the reference has no fault-injection tooling;
+    SURVEY.md 5.2/5.3 asks for randomised delays): 8 workers, thReduce = thComplete = 0.75, online-nodes gate
+    6 of 8, maxLag 4, and every round a random subset of workers is late or silent.  Each worker's message is
+    the constant 2^rank, so a reduced value is the bitmask of its contributors: on every rank, for every
+    element, popcount(value) must equal the reported count, and count 0 must come with value 0."""
+    import random
+
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    P, n = 8, 1 << 15
+    cl = _cluster(P, n, 1 << 11, max_lag=4, th_reduce=0.75, th_complete=0.75, th_allreduce=0.75, timeout_ms=200)
+    srcs = [torch.full((n,), float(1 << r), device="cuda") for r in range(P)]
+    rng = random.Random(7)
+    seen = set()
+    for r in range(120):
+        late = rng.sample(range(P), rng.choice([0, 0, 1, 2]))
+        inj = Injection(delay_ns={k: rng.choice([20_000, 200_000, 2_000_000]) for k in late[:1]},
+                        mute=sum(1 << k for k in late[1:]))
+        outs, counts = cl.run_round(srcs, inj)
+        torch.cuda.synchronize()
+        for i in range(P):
+            bits = outs[i].to(torch.int64)
+            pop = sum(((bits >> b) & 1) for b in range(P))
+            assert torch.equal(pop, counts[i].to(torch.int64)), f"round {r} rank {i}"
+            assert bool((bits.to(torch.float32) == outs[i]).all())
+        seen.update(counts[0].unique().tolist())
+    assert seen <= {0, 6, 7, 8} and 8 in seen and (6 in seen or 7 in seen)
+    assert cl.done_tags() == [120] * P
