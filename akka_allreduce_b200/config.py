@@ -272,4 +272,8 @@ def load_config(path: str | Path | None = None, overrides: dict | None = None) -
     return cfg
 
 
-DEFAULT_CONFIG_PATH = Path(__file__).resolve().parent.parent / "conf" / "application.conf"
+# Two identical copies, like the reference's src/main/resources/application.conf and conf/application.conf:
+# the one in conf/ is for editing in a checkout, the packaged one travels with an installed package.
+PACKAGED_CONFIG_PATH = Path(__file__).resolve().parent / "resources" / "application.conf"
+_checkout_conf = Path(__file__).resolve().parent.parent / "conf" / "application.conf"
+DEFAULT_CONFIG_PATH = _checkout_conf if _checkout_conf.exists() else PACKAGED_CONFIG_PATH

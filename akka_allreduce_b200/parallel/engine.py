@@ -128,7 +128,8 @@ class DeviceAllreduce:
     def input_view(self, round_: int) -> torch.Tensor | None:
         """Tensor aliasing the staging slot of ``round_`` (NVLS mode only: there the scatter stages the
         message locally and the switch pulls it).  A source written here needs no copy at all."""
-        if not (self.zero_copy_ok and self.algo == "nvls"):
+        # (push mode stages nothing locally — except with a single rank, whose own scat row IS the staging slot)
+        if not (self.zero_copy_ok and (self.algo == "nvls" or self.world == 1)):
             return None
         l, g = self.launcher, self.geo
         esz = torch.empty((), dtype=l.wire_dtype).element_size()

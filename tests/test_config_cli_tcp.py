@@ -29,6 +29,13 @@ def test_default_config_file_matches_reference_hardcoded_values():
     assert c.cluster.port == 2551 and c.cluster.downAfter == 10.0
 
 
+def test_packaged_config_copy_is_identical():
+    """The reference ships two byte-identical copies of its config (src/main/resources and conf/); so do we."""
+    from akka_allreduce_b200.config import PACKAGED_CONFIG_PATH
+
+    assert PACKAGED_CONFIG_PATH.read_bytes() == DEFAULT_CONFIG_PATH.read_bytes()
+
+
 def test_reference_akka_conf_is_accepted(tmp_path):
     """The reference's own application.conf parses; port/loglevel/auto-down are picked up."""
     ref = "/root/reference/src/main/resources/application.conf"
