@@ -33,6 +33,8 @@ def main():
     ap.add_argument("--tiny", action="store_true")
     ap.add_argument("--bucket-mb", type=int, default=25)
     ap.add_argument("--out", default="")
+    ap.add_argument("--ctas", type=int, default=0, help="work CTAs of the comm kernel (0 = hook default)")
+    ap.add_argument("--skip-nccl", action="store_true")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -56,11 +58,11 @@ def main():
         return float(t.item())
 
     results, grads = {}, {}
-    for variant in ("nccl", "fused_hook"):
+    for variant in (("fused_hook",) if args.skip_nccl else ("nccl", "fused_hook")):
         model = DDP(build(), device_ids=[local], bucket_cap_mb=args.bucket_mb, gradient_as_bucket_view=True)
         hook = None
         if variant == "fused_hook":
-            hook = AllreduceCommHook(rank, world, local)
+            hook = AllreduceCommHook(rank, world, local, ctas=args.ctas or None)
             model.register_comm_hook(None, hook)
         opt = torch.optim.AdamW(model.parameters(), lr=1e-4, fused=True)
         times = []
@@ -90,6 +92,12 @@ def main():
             hook.close()
         del model, opt
         torch.cuda.empty_cache()
+    if args.skip_nccl:
+        if rank == 0:
+            print(json.dumps({"ctas": args.ctas, **results}), flush=True)
+        dist.barrier()
+        dist.destroy_process_group()
+        return 0
     diff = float((grads["nccl"] - grads["fused_hook"]).abs().max())
     scale = float(grads["nccl"].abs().max())
     out = {"model": "gpt2-tiny" if args.tiny else "gpt2-small", "params": sum(p.numel() for p in build().parameters()),

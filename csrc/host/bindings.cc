@@ -274,6 +274,10 @@ PYBIND11_MODULE(_aar_host, m) {
       .def("send", [](PyBus& b, Endpoint to, Message msg) { b.bus.send(to, std::move(msg)); })
       .def("run", [](PyBus& b, size_t max_steps) { return b.bus.run(max_steps); },
            py::arg("max_steps") = size_t(1) << 22)
+      .def("set_chaos", [](PyBus& b, uint64_t seed, double drop, double delay) { b.bus.set_chaos(seed, drop, delay); },
+           py::arg("seed"), py::arg("drop") = 0.0, py::arg("delay") = 0.0,
+           "Drop / reorder data messages in transit (deterministic fault injection for tests)")
+      .def("chaos_dropped", [](PyBus& b) { return b.bus.chaos_dropped(); })
       .def("pending", [](PyBus& b) { return b.bus.pending(); })
       .def("dropped", [](PyBus& b) { return b.bus.dropped(); })
       .def("take",

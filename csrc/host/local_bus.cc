@@ -18,12 +18,30 @@ Endpoint LocalBus::add_probe() {
 
 void LocalBus::send(Endpoint to, Message msg) { queue_.emplace_back(to, std::move(msg)); }
 
+double LocalBus::next_uniform() {  // xorshift64*: small, seedable, good enough for fault injection
+  rng_state_ ^= rng_state_ >> 12;
+  rng_state_ ^= rng_state_ << 25;
+  rng_state_ ^= rng_state_ >> 27;
+  return static_cast<double>((rng_state_ * 0x2545F4914F6CDD1Dull) >> 11) / 9007199254740992.0;
+}
+
 size_t LocalBus::run(size_t max_steps) {
   size_t steps = 0;
   while (!queue_.empty() && steps < max_steps) {
     auto [to, msg] = std::move(queue_.front());
     queue_.pop_front();
     ++steps;
+    if (rng_state_ != 0 && (kind_of(msg) == MsgKind::Scatter || kind_of(msg) == MsgKind::Reduce)) {
+      const double u = next_uniform();
+      if (u < drop_) {
+        ++chaos_dropped_;
+        continue;
+      }
+      if (u < drop_ + delay_ && !queue_.empty()) {
+        queue_.emplace_back(to, std::move(msg));
+        continue;
+      }
+    }
     if (auto box = inboxes_.find(to); box != inboxes_.end()) {
       box->second.push_back(std::move(msg));
     } else if (auto h = handlers_.find(to); h != handlers_.end()) {

@@ -29,6 +29,17 @@ class LocalBus : public Mailer {
   size_t run(size_t max_steps = 1u << 22);
   size_t pending() const { return queue_.size(); }
 
+  // Fault injection for tests (the reference has none): every ScatterBlock / ReduceBlock in
+  // transit is dropped with probability `drop` or pushed back to the end of the queue with probability
+  // `delay` (reordering across senders; per-pair FIFO is NOT preserved for delayed messages).  Control
+  // messages (Init/Start/Complete) always get through.  Deterministic for a given seed.
+  void set_chaos(uint64_t seed, double drop, double delay) {
+    rng_state_ = seed ? seed : 0x9e3779b97f4a7c15ull;
+    drop_ = drop;
+    delay_ = delay;
+  }
+  size_t chaos_dropped() const { return chaos_dropped_; }
+
   std::vector<Message>& inbox(Endpoint probe) { return inboxes_[probe]; }
   size_t dropped() const { return dropped_; }
 
@@ -38,6 +49,10 @@ class LocalBus : public Mailer {
   std::map<Endpoint, std::vector<Message>> inboxes_;
   std::deque<std::pair<Endpoint, Message>> queue_;
   size_t dropped_ = 0;
+  double next_uniform();
+  uint64_t rng_state_ = 0;
+  double drop_ = 0.0, delay_ = 0.0;
+  size_t chaos_dropped_ = 0;
 };
 
 }  // namespace aar
