@@ -197,3 +197,9 @@ def test_tcp_replacement_worker_rejoins():
     rounds = [r for r, _ in seen["replacement"]]
     assert rounds and min(rounds) >= 20          # joined at the current round
     assert any(c > 0 for r, c in seen[0] if r > min(rounds) + 5)   # block 3 is being reduced again
+
+
+def test_quickstart_example_runs():
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "quickstart_cpu.py")], capture_output=True,
+                       text=True, timeout=120, env=dict(os.environ, PYTHONPATH=ROOT))
+    assert p.returncode == 0 and p.stdout.strip().startswith("ok:"), p.stdout[-500:] + p.stderr[-1500:]
