@@ -65,6 +65,8 @@ class RoundLauncher:
         self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.force_offset = self.lib.aar_scratch_force_offset(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.launches = 0
+        self._prepared: set[int] = set()   # launch structs (by id) whose static fields are filled
+        self._injected: set[int] = set()   # launch structs that still carry last round's straggler injection
 
     def prepare(self, a: K.AarLaunch) -> None:
         """Fills everything that does not change from round to round (done once per launch struct)."""
@@ -94,21 +96,22 @@ class RoundLauncher:
         for r in range(K.MAX_RANKS):
             a.skip_dest_mask[r] = 0
             a.delay_ns[r] = 0
-        a._aar_prepared = True
-        a._aar_injected = False
+        self._prepared.add(id(a))
+        self._injected.discard(id(a))
 
     def fill(self, a: K.AarLaunch, round_: int, inj: Injection | None) -> None:
         """Per-round fields only: ring slot, round tag and (rarely) the straggler injection."""
-        if not getattr(a, "_aar_prepared", False):
+        if id(a) not in self._prepared:
             self.prepare(a)
         a.slot, a.tag = round_ % self.geo.slots, round_ + 1
-        if inj is not None or a._aar_injected:
+        if inj is not None or id(a) in self._injected:  # set this round's injection / clear last round's
             a.mute_mask = 0
             for r in range(K.MAX_RANKS):
                 a.skip_dest_mask[r] = 0
                 a.delay_ns[r] = 0
-            a._aar_injected = inj is not None
+            self._injected.discard(id(a))
             if inj is not None:
+                self._injected.add(id(a))
                 a.mute_mask = inj.mute
                 for r, m in inj.skip.items():
                     a.skip_dest_mask[r] = m

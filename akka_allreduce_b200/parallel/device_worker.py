@@ -34,6 +34,15 @@ from .engine import DeviceAllreduce, default_uds_dir
 _DTYPES = {"float32": torch.float32, "bfloat16": torch.bfloat16}
 
 
+class SinkStats:
+    """What the built-in throughput/assert sink has seen (mirror of the CPU backend's ThroughputStats)."""
+
+    def __init__(self) -> None:
+        self.checkpoints = 0
+        self.failures = 0
+        self.last_mbytes_per_s = 0.0
+
+
 class DeviceWorker:
     def __init__(self, data_source: DataSource, data_sink: DataSink, config: AllreduceConfig,
                  master_host: str | None = None, master_port: int | None = None, device: int | None = None,
@@ -216,7 +225,8 @@ class DeviceWorker:
 # ---- built-in benchmark source/sink (AllreduceWorker.scala:324-343) ------------------------------
 def start_device_worker(config: AllreduceConfig, data_size: int, checkpoint: int = 50, assert_multiple: int = 0,
                         master_host: str | None = None, master_port: int | None = None) -> DeviceWorker:
-    state = {"ramp": None, "tic": time.time(), "failures": 0}
+    state = {"ramp": None, "tic": time.time()}
+    stats = SinkStats()
     log = get_logger("worker")
 
     def source(req: AllReduceInputRequest) -> AllReduceInput:
@@ -231,6 +241,8 @@ def start_device_worker(config: AllreduceConfig, data_size: int, checkpoint: int
         mbytes = out.data.numel() * 4.0 * checkpoint / 1e6
         print(f"----Data output at #{out.iteration} - {elapsed} s")
         print("%2.1f Mbytes in %2.1f seconds at %4.3f MBytes/sec" % (mbytes, elapsed, mbytes / elapsed), flush=True)
+        stats.checkpoints += 1
+        stats.last_mbytes_per_s = mbytes / elapsed
         world = config.worker.totalSize
         if world > 1:  # bus bandwidth, nccl-tests convention: algbw x 2(P-1)/P
             esz = out.data.element_size()
@@ -240,12 +252,12 @@ def start_device_worker(config: AllreduceConfig, data_size: int, checkpoint: int
         if assert_multiple > 0:
             ok = bool((out.data == state["ramp"] * assert_multiple).all()) and bool((out.count == assert_multiple).all())
             if not ok:
-                state["failures"] += 1
+                stats.failures += 1
                 log.error("Expected output should be multiple of input, counts equal to the multiple. "
                           "Check if all thresholds are 1 (iteration %d)", out.iteration)
         state["tic"] = time.time()
 
     w = DeviceWorker(source, sink, config, master_host, master_port)
-    w.stats = type("Stats", (), {"failures": property(lambda self: state["failures"])})()
+    w.stats = stats
     w.start()
     return w

@@ -37,13 +37,17 @@ class AllreduceWorker:
 
     def __init__(self, data_source: DataSource | None, data_sink: DataSink | None,
                  master_host: str = "127.0.0.1", master_port: int = 2551, port: int = 0,
-                 heartbeat: float = 1.0, loglevel: str = "INFO"):
+                 heartbeat: float = 1.0, loglevel: str = "INFO", _node=None, _stats=None):
         self.log = get_logger("worker", loglevel)
-        opts = host.WorkerNodeOptions()
-        opts.heartbeat_s = heartbeat
-        self._stats = None
+        self._stats = _stats
+        self._port = port
+        if _node is not None:  # built by `builtin()`
+            self._node = _node
+            return
         if data_source is None or data_sink is None:
             raise ValueError("AllreduceWorker needs a data source and a data sink")
+        opts = host.WorkerNodeOptions()
+        opts.heartbeat_s = heartbeat
 
         def source(iteration: int):
             out = data_source(AllReduceInputRequest(iteration))
@@ -53,22 +57,17 @@ class AllreduceWorker:
             data_sink(AllReduceOutput(data, count, iteration))
 
         self._node = host.WorkerNode(master_host, master_port, source, sink, opts)
-        self._port = port
 
     @classmethod
     def builtin(cls, data_size: int, checkpoint: int = 50, assert_multiple: int = 0,
                 master_host: str = "127.0.0.1", master_port: int = 2551, port: int = 0,
                 heartbeat: float = 1.0) -> "AllreduceWorker":
         """Worker with the native ramp source and throughput/assert sink (no Python per round)."""
-        self = cls.__new__(cls)
-        self.log = get_logger("worker")
         opts = host.WorkerNodeOptions()
         opts.heartbeat_s = heartbeat
-        self._stats = host.ThroughputStats()
-        self._node = host.WorkerNode.builtin(master_host, master_port, data_size, checkpoint, assert_multiple,
-                                             self._stats, opts)
-        self._port = port
-        return self
+        stats = host.ThroughputStats()
+        node = host.WorkerNode.builtin(master_host, master_port, data_size, checkpoint, assert_multiple, stats, opts)
+        return cls(None, None, master_host, master_port, port, heartbeat, _node=node, _stats=stats)
 
     def start(self) -> int:
         port = self._node.listen("127.0.0.1", self._port)

@@ -86,8 +86,8 @@ def distributed(args) -> dict:
 
     def source(req):
         nonlocal mine
-        if mine is None:
-            mine = torch.full((args.size,), float(1 << state["id"]), device=dev)
+        if mine is None:  # the worker id (= bit of this rank's contribution) is assigned by the master at InitWorkers
+            mine = torch.full((args.size,), float(1 << w.id), device=dev)
         if rank in stragglers and rng.random() < args.straggle_prob:
             time.sleep(args.delay_us * 1e-6)                     # a slow data source = a straggling worker
         return AllReduceInput(mine)
@@ -103,16 +103,6 @@ def distributed(args) -> dict:
             state["zero_elems"] += int((out.count == 0).sum())
 
     w = DeviceWorker(source, sink, cfg, master_port=cfg.cluster.port, device=local)
-    orig = w._run
-
-    def run_with_id():
-        # the worker id (= bit of this rank's contribution) is only known after InitWorkers
-        while w._init is None and not w._stop:
-            time.sleep(0.001)
-        state["id"] = w._init.dest_id if w._init is not None else 0
-        orig()
-
-    w._run = run_with_id
     dist.barrier()
     w.start()
     finished = w.wait(600)
