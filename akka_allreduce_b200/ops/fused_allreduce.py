@@ -65,6 +65,9 @@ class RoundLauncher:
         self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.force_offset = self.lib.aar_scratch_force_offset(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.launches = 0
+        # one-shot flavour: 0 push (default), 1 pull with in-switch reduce, 2 pull with unicast loads (opt-in:
+        # written after the round's multi-GPU budget was spent, validated in emulation only — see DESIGN.md 7)
+        self.oneshot_pull = int(os.environ.get("AAR_ONESHOT_PULL", 0))
         self._prepared: set[int] = set()   # launch structs (by id) whose static fields are filled
         self._injected: set[int] = set()   # launch structs that still carry last round's straggler injection
 
@@ -80,6 +83,7 @@ class RoundLauncher:
         # On for messages of 512 MB and more.  AAR_OVERLAP=1/0 forces it.
         ov = os.environ.get("AAR_OVERLAP")
         a.overlap_flush = int(ov) if ov in ("0", "1") else (1 if g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20) else 0)
+        a.oneshot_pull = self.oneshot_pull
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))

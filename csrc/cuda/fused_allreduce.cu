@@ -847,9 +847,16 @@ __global__ void __launch_bounds__(kThreads, 1) aar_twoshot_kernel(const __grid_c
 // own arrival flag per sender, so CTAs never talk to each other.  All ranks add the same values in
 // the same order, so they still end up bit-identical (what the owner-reduces rule gives the two-shot
 // path).  A sender that does not show up before the timeout is left out and the count says so.
-template <typename TIn, typename TW>
+//
+// kPull selects the pull form of the same idea: every rank only STAGES its slice in its own one-shot row
+// 0 (a local copy, so a gpu-scope fence orders it) and raises its flag on the peers; each rank then sums
+// the P staged copies by reading them over NVLink — with a multicast alias as ONE multimem.ld_reduce per
+// 16 bytes (the switch adds the P copies), otherwise with P unicast loads.  No system-scope fence and no
+// second hop; the price is P x N bytes leaving every GPU, so it is meant for the 0.5-2 MB range.
+template <typename TIn, typename TW, bool kPull>
 __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_constant__ KParams p) {
   __shared__ uint32_t sh_mask;
+  __shared__ const TW* sh_rows[kMaxRanks];
   const int vr = p.a.emu ? blockIdx.y : 0;
   const int rank = p.a.emu ? static_cast<int>(blockIdx.y) : p.a.rank;
   const int P = p.a.world, slot = p.a.slot;
@@ -889,18 +896,26 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
   const bool muted = (p.a.mute_mask >> rank) & 1u;
   const uint32_t skip = p.a.skip_dest_mask[rank];
 
-  // ---- push my slice to every peer (self first), then raise my flag there
+  // ---- push my slice to every peer (self first) — or, pull form, stage it once locally — then raise my flag
   if (len > 0 && !muted) {
-    for (int i = 0; i < P; ++i) {
-      const int q = (i + rank) % P;
-      if ((skip >> q) & 1u) continue;
-      TW* dst = reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_os) + p.sym.os_elem(slot, rank) + lo;
+    if (kPull) {
+      TW* dst = reinterpret_cast<TW*>(my_sym + p.sym.off_os) + p.sym.os_elem(slot, 0) + lo;
       push_tile<TIn, TW>(src + lo, dst, len, p.a.scale, vec);
+    } else {
+      for (int i = 0; i < P; ++i) {
+        const int q = (i + rank) % P;
+        if ((skip >> q) & 1u) continue;
+        TW* dst = reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_os) + p.sym.os_elem(slot, rank) + lo;
+        push_tile<TIn, TW>(src + lo, dst, len, p.a.scale, vec);
+      }
     }
   }
+  if (threadIdx.x < P)  // where sender s's copy of my slice lives: its own staging row (pull) or my row s (push)
+    sh_rows[threadIdx.x] = kPull ? reinterpret_cast<const TW*>(p.a.sym[threadIdx.x] + p.sym.off_os) + p.sym.os_elem(slot, 0) + lo
+                                 : reinterpret_cast<const TW*>(my_sym + p.sym.off_os) + p.sym.os_elem(slot, threadIdx.x) + lo;
   __syncthreads();
   if (threadIdx.x == 0 && !muted) {
-    if (p.a.fast_fences) __threadfence();
+    if (p.a.fast_fences || kPull) __threadfence();  // staged locally: the peers read it through this GPU's L2
     else __threadfence_system();  // the slices must have landed on the peers before the flags do
     for (int i = 0; i < P; ++i) {
       const int q = (i + rank) % P;
@@ -932,12 +947,43 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
   const int cnt = __popc(mask);
   const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
   if (len > 0) {
-    const TW* row0 = reinterpret_cast<const TW*>(my_sym + p.sym.off_os) + p.sym.os_elem(slot, 0) + lo;
     constexpr int E = 16 / (sizeof(TIn) > sizeof(TW) ? sizeof(TIn) : sizeof(TW));
     using UW = Unit<TW, E>;
     using UO = Unit<TIn, E>;
     int done = 0;
-    if (vec) {
+    const uint32_t all_ranks = (1u << P) - 1u;
+    if (kPull && vec && sizeof(typename UW::raw_t) == 16 && p.a.mc_base != nullptr && p.a.oneshot_pull == 1 &&
+        mask == all_ranks) {
+      // in-switch reduction of the P staged copies: one request per 16 bytes, eight in flight per thread
+      const int units = len / E;
+      const uint4* mc = reinterpret_cast<const uint4*>(
+          p.a.mc_base + p.sym.off_os + (p.sym.os_elem(slot, 0) + lo) * static_cast<int64_t>(sizeof(TW)));
+      for (int u0 = threadIdx.x; u0 < units; u0 += kThreads * 8) {
+        uint4 r[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int u = u0 + j * kThreads;
+          if (u < units) r[j] = multimem_ld_reduce_add<TW>(mc + u);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int u = u0 + j * kThreads;
+          if (u < units) {
+            float v[E];
+            UW::unpack(*reinterpret_cast<const typename UW::raw_t*>(&r[j]), v);
+#pragma unroll
+            for (int e = 0; e < E; ++e) v[e] *= post;
+            reinterpret_cast<typename UO::raw_t*>(out + lo)[u] = UO::pack(v);
+            if (counts != nullptr) {
+              int4* cp = reinterpret_cast<int4*>(counts + lo + static_cast<int64_t>(u) * E);
+#pragma unroll
+              for (int e = 0; e < E / 4; ++e) cp[e] = make_int4(cnt, cnt, cnt, cnt);
+            }
+          }
+        }
+      }
+      done = units * E;
+    } else if (vec) {
       const int units = len / E;
       for (int u = threadIdx.x; u < units; u += kThreads) {
         float acc[E];
@@ -948,8 +994,7 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const int s = s0 + j;
-            if (s < P && ((mask >> s) & 1u))
-              r[j] = ld_fresh(reinterpret_cast<const typename UW::raw_t*>(row0 + static_cast<int64_t>(s) * p.sym.os_cap) + u);
+            if (s < P && ((mask >> s) & 1u)) r[j] = ld_fresh(reinterpret_cast<const typename UW::raw_t*>(sh_rows[s]) + u);
           }
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
@@ -976,7 +1021,7 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
     for (int i = done + threadIdx.x; i < len; i += kThreads) {
       float acc = 0.f;
       for (int s = 0; s < P; ++s)
-        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(row0 + static_cast<int64_t>(s) * p.sym.os_cap + i));
+        if ((mask >> s) & 1u) acc += to_float(ld_fresh_scalar(sh_rows[s] + i));
       out[lo + i] = from_float<TIn>(acc * post);
       if (counts != nullptr) counts[lo + i] = cnt;
     }
@@ -1035,11 +1080,12 @@ int launch_oneshot(const KParams& kp, cudaStream_t stream) {
   if (nct < 1) nct = 1;
   dim3 grid(nct, kp.a.emu ? kp.a.world : 1);
   cudaError_t e;
+  auto* fn = kp.a.oneshot_pull ? aar_oneshot_kernel<TIn, TW, true> : aar_oneshot_kernel<TIn, TW, false>;
   if (kp.a.emu) {
     void* args[] = {const_cast<KParams*>(&kp)};
-    e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(aar_oneshot_kernel<TIn, TW>), grid, dim3(kThreads), args, 0, stream);
+    e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(fn), grid, dim3(kThreads), args, 0, stream);
   } else {
-    aar_oneshot_kernel<TIn, TW><<<grid, kThreads, 0, stream>>>(kp);
+    fn<<<grid, kThreads, 0, stream>>>(kp);
     e = cudaGetLastError();
   }
   if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("one-shot launch: ") + cudaGetErrorString(e));

@@ -37,6 +37,8 @@ typedef struct AarLaunch {
   int32_t nvls_unroll;      /* multimem.ld_reduce requests in flight per thread: 0/8 = 8, or 16 */
   int32_t part_kb;          /* largest work item in KB of wire data; 0 = 256 */
   int32_t overlap_flush;    /* 1: flush already-delivered chunks between reduce items (overlaps phases R and C) */
+  int32_t oneshot_pull;     /* one-shot only. 0: push copies to every peer; 1: stage locally, peers pull (in-switch
+                               multimem.ld_reduce when mc_base is set); 2: stage locally, unicast pulls only */
   int64_t n, max_chunk;     /* dataSize, maxChunkSize (elements) */
   int64_t os_cap;           /* one-shot capacity the region was laid out with */
   int64_t block_step;       /* 0 = reference partition ceil(n/world); else an aligned step >= that */

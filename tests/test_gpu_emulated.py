@@ -327,3 +327,27 @@ def test_random_straggler_stress_counts_always_explain_the_sums():
         seen.update(counts[0].unique().tolist())
     assert seen <= {0, 6, 7, 8} and 8 in seen and (6 in seen or 7 in seen)
     assert cl.done_tags() == [120] * P
+
+
+@pytest.mark.parametrize("world,n", [(8, 256), (4, 778), (8, 1 << 18), (5, 100003)])
+def test_oneshot_pull_variant(world, n, monkeypatch):
+    """Pull form of the one-shot round (stage locally, peers read it; opt-in via AAR_ONESHOT_PULL): same sums,
+    same counts, ring wrap.  (On one GPU there is no multicast alias, so this runs its unicast-pull path.)"""
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    monkeypatch.setenv("AAR_ONESHOT_PULL", "2")
+    cl = _cluster(world, n, max(1, n // 3), max_lag=1, algo="oneshot", timeout_ms=5000)
+    assert cl.launcher.oneshot_pull == 2
+    for r in range(5):
+        srcs = _srcs(world, n, torch.float32, 40 + r)
+        outs, counts = cl.run_round(srcs)
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i], want) and bool((counts[i] == world).all())
+    assert cl.timeouts_seen() == [0] * world
+    # a silent rank is left out after the bounded wait, and the count says so
+    cl2 = _cluster(4, 4096, 1024, algo="oneshot", timeout_ms=20)
+    srcs = _srcs(4, 4096, torch.float32, 2)
+    outs, counts = cl2.run_round(srcs, Injection(mute=1 << 1))
+    want = _ref_sum(srcs, ranks=[0, 2, 3])
+    assert all(torch.equal(outs[i], want) and bool((counts[i] == 3).all()) for i in range(4))
