@@ -14,7 +14,7 @@ __version__ = "0.1.0"
 __all__ = [
     "AllReduceInput", "AllReduceInputRequest", "AllReduceOutput", "DataSink", "DataSource",
     "AllreduceConfig", "ClusterConfig", "DataConfig", "DeviceConfig", "ThresholdConfig", "WorkerConfig",
-    "load_config", "AllreduceMaster", "AllreduceWorker",
+    "load_config", "AllreduceMaster", "AllreduceWorker", "create_worker",
 ]
 
 
@@ -27,4 +27,8 @@ def __getattr__(name):  # lazy: importing the package must not trigger a native 
         from .worker import AllreduceWorker
 
         return AllreduceWorker
+    if name == "create_worker":
+        from .worker import create_worker
+
+        return create_worker
     raise AttributeError(name)

@@ -87,6 +87,21 @@ class AllreduceWorker:
     engine = property(lambda self: self._node.engine)
 
 
+def create_worker(data_source: DataSource, data_sink: DataSink, config: AllreduceConfig,
+                  master_host: str | None = None, master_port: int | None = None, **kwargs):
+    """One constructor for both backends: ``config.device.backend`` picks the CPU worker (C++ protocol engine
+    over TCP) or the CUDA worker (fused kernel over NVLink); the callbacks and the contract are the same."""
+    host_, port_ = master_host or config.cluster.host, master_port or config.cluster.port
+    if config.device.backend == "cuda":
+        from .parallel.device_worker import DeviceWorker
+
+        return DeviceWorker(data_source, data_sink, config, host_, port_, **kwargs)
+    if config.device.backend != "cpu":
+        raise ValueError(f"unknown backend {config.device.backend!r} (cpu | cuda)")
+    return AllreduceWorker(data_source, data_sink, host_, port_, heartbeat=config.cluster.heartbeat,
+                           loglevel=config.cluster.loglevel, **kwargs)
+
+
 def ramp_source(data_size: int) -> DataSource:
     floats = np.arange(data_size, dtype=np.float32)
     return lambda req: AllReduceInput(floats)
