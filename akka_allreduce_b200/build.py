@@ -139,6 +139,26 @@ def build_host(force: bool = False) -> Path:
     return out
 
 
+def build_cpu_cluster(force: bool = False) -> Path:
+    """Stand-alone binary of the CPU backend (coordinator + N workers in one process, no Python):
+    ``build/aar_cpu_cluster [numOfWorkers dataSize maxChunkSize maxRound maxLag thAllreduce thReduce thComplete]``."""
+    out = ROOT / "build" / "aar_cpu_cluster"
+    core = ["host/buffers.cc", "host/worker_engine.cc", "host/master_engine.cc", "host/local_bus.cc", "host/node.cc",
+            "host/cpu_cluster_main.cc"]
+    srcs = [CSRC / s for s in core]
+    deps = srcs + _headers()
+    if not force and not _stale(out, deps):
+        return out
+    with _BuildLock():
+        (ROOT / "build").mkdir(exist_ok=True)
+        tmp = out.with_suffix(".tmp%d" % os.getpid())
+        _run(["g++", "-std=c++17", "-O2", "-Wall", "-Wno-unused-parameter", f"-I{INCLUDE}", f"-I{CSRC / 'host'}",
+              "-o", str(tmp)] + [str(s) for s in srcs] + ["-lpthread"])
+        os.replace(tmp, out)
+        _record(out, deps)
+    return out
+
+
 def nvcc_path() -> str | None:
     cand = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     return cand if Path(cand).exists() else None

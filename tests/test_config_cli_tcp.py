@@ -203,3 +203,15 @@ def test_quickstart_example_runs():
     p = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "quickstart_cpu.py")], capture_output=True,
                        text=True, timeout=120, env=dict(os.environ, PYTHONPATH=ROOT))
     assert p.returncode == 0 and p.stdout.strip().startswith("ok:"), p.stdout[-500:] + p.stderr[-1500:]
+
+
+def test_native_cpu_cluster_binary():
+    """The host runtime stands alone: coordinator + workers in one native process (no Python in the loop),
+    reference defaults (2 workers, dataSize 10, maxChunkSize 2, th 1/1/0.8) and the 4-worker manual config with
+    the assertMultiple check."""
+    from akka_allreduce_b200.build import build_cpu_cluster
+
+    exe = str(build_cpu_cluster())
+    for argv in (["2", "10", "2", "500", "1", "1", "1", "0.8"], ["4", "778", "3", "200", "3", "1", "1", "1"]):
+        p = subprocess.run([exe] + argv, capture_output=True, text=True, timeout=120)
+        assert p.returncode == 0 and "finished:" in p.stdout and "0 sink assertion failures" in p.stdout, p.stdout + p.stderr
