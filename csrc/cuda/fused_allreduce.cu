@@ -30,6 +30,7 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <atomic>
 #include <mutex>
 #include <string>
 
@@ -1043,6 +1044,7 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
 }
 
 // ---------------------------------------------------------------- host side
+constexpr int kMaxDevices = 64;
 thread_local std::string g_error;
 int fail(int code, const std::string& what) {
   g_error = what;
@@ -1052,11 +1054,14 @@ int fail(int code, const std::string& what) {
 template <typename TIn, typename TW, bool kNvls>
 int launch_twoshot(const KParams& kp, cudaStream_t stream) {
   auto* fn = aar_twoshot_kernel<TIn, TW, kNvls>;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  // The shared-memory opt-in is a per-device attribute of the function: once per (instantiation, device).
+  static std::atomic<bool> configured[kMaxDevices];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return fail(AAR_ECUDA, "cudaGetDevice failed");
+  if (dev >= kMaxDevices || !configured[dev].load(std::memory_order_acquire)) {
     cudaError_t ea = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
     if (ea != cudaSuccess) return fail(AAR_ECUDA, std::string("cudaFuncSetAttribute(smem): ") + cudaGetErrorString(ea));
-    configured = true;
+    if (dev < kMaxDevices) configured[dev].store(true, std::memory_order_release);
   }
   const int smem = kp.a.use_tma ? kSmemBytes : 0;
   dim3 grid(kp.a.ctas + 1, kp.a.emu ? kp.a.world : 1);

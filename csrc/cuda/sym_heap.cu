@@ -24,6 +24,7 @@
 #include <time.h>
 #include <unistd.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -65,11 +66,8 @@ bool resolve(const char* name, F& fn) {
   return true;
 }
 
-Driver& driver() {
-  static Driver d;
-  static bool tried = false;
-  if (tried) return d;
-  tried = true;
+Driver resolve_driver() {
+  Driver d;
   bool ok = true;
   ok &= resolve("cuMemCreate", d.MemCreate);
   ok &= resolve("cuMemRelease", d.MemRelease);
@@ -90,6 +88,11 @@ Driver& driver() {
   resolve("cuMulticastBindMem", d.MulticastBindMem);
   resolve("cuMulticastGetGranularity", d.MulticastGetGranularity);
   d.ok = ok;
+  return d;
+}
+
+Driver& driver() {
+  static Driver d = resolve_driver();  // initialised once, thread-safe
   return d;
 }
 
@@ -279,13 +282,20 @@ static int map_handle(AarHeap* h, CUmemGenericAllocationHandle handle, CUdevicep
   CUresult r = d.MemAddressReserve(&va, h->bytes, 0, 0, 0);
   if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemAddressReserve: " + cu_err(r));
   r = d.MemMap(va, h->bytes, 0, handle, 0);
-  if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemMap: " + cu_err(r));
+  if (r != CUDA_SUCCESS) {
+    d.MemAddressFree(va, h->bytes);
+    return fail(AAR_ECUDA, "cuMemMap: " + cu_err(r));
+  }
   CUmemAccessDesc acc{};
   acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   acc.location.id = h->device;
   acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
   r = d.MemSetAccess(va, h->bytes, &acc, 1);
-  if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemSetAccess: " + cu_err(r));
+  if (r != CUDA_SUCCESS) {
+    d.MemUnmap(va, h->bytes);
+    d.MemAddressFree(va, h->bytes);
+    return fail(AAR_ECUDA, "cuMemSetAccess: " + cu_err(r));
+  }
   *out = va;
   return AAR_OK;
 }
@@ -303,14 +313,18 @@ int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t byte
   h->device = device;
   h->va.assign(world, 0);
   h->imported.assign(world, 0);
+  // Every early return below goes through this: whatever was created, mapped or imported so far is undone.
+  struct Cleanup {
+    AarHeap* h;
+    ~Cleanup() {
+      if (h != nullptr) aar_heap_destroy(h);
+    }
+  } cleanup{h};
 
   std::string err;
-  static int heap_seq = 0;
-  SideChannel ch(rank, world, uds_dir ? uds_dir : "/tmp", heap_seq++);
-  if (world > 1 && !ch.open_socket(err)) {
-    delete h;
-    return fail(AAR_ECUDA, err);
-  }
+  static std::atomic<int> heap_seq{0};
+  SideChannel ch(rank, world, uds_dir ? uds_dir : "/tmp", heap_seq.fetch_add(1));
+  if (world > 1 && !ch.open_socket(err)) return fail(AAR_ECUDA, err);
 
   // ---- can this platform export VMM handles as file descriptors? (agreed by all ranks)
   int vmm_ok = 0, mc_ok = 0;
@@ -327,10 +341,7 @@ int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t byte
   if (getenv("AAR_HEAP_FORCE_IPC") != nullptr) vmm_ok = 0;
   if (world > 1) {
     int agreed = 0;
-    if (!ch.agree_min(vmm_ok * 2 + (vmm_ok ? mc_ok : 0), agreed, err)) {
-      delete h;
-      return fail(AAR_ECUDA, err);
-    }
+    if (!ch.agree_min(vmm_ok * 2 + (vmm_ok ? mc_ok : 0), agreed, err)) return fail(AAR_ECUDA, err);
     vmm_ok = agreed >= 2;
     mc_ok = agreed == 3;
   }
@@ -345,10 +356,7 @@ int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t byte
   if (h->vmm) {
     size_t gran = 0;
     CUresult r = d.MemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED);
-    if (r != CUDA_SUCCESS) {
-      delete h;
-      return fail(AAR_ECUDA, "cuMemGetAllocationGranularity: " + cu_err(r));
-    }
+    if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemGetAllocationGranularity: " + cu_err(r));
     CUmulticastObjectProp mprop{};
     if (mc_ok) {
       mprop.numDevices = static_cast<unsigned>(world);
@@ -360,10 +368,7 @@ int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t byte
     }
     h->bytes = round_up(static_cast<size_t>(bytes), gran);
     r = d.MemCreate(&h->local, h->bytes, &prop, 0);
-    if (r != CUDA_SUCCESS) {
-      delete h;
-      return fail(AAR_ECUDA, "cuMemCreate(" + std::to_string(h->bytes) + "): " + cu_err(r));
-    }
+    if (r != CUDA_SUCCESS) return fail(AAR_ECUDA, "cuMemCreate(" + std::to_string(h->bytes) + "): " + cu_err(r));
     int rc = map_handle(h, h->local, &h->va[rank]);
     if (rc != AAR_OK) return rc;
     if (cudaMemset(reinterpret_cast<void*>(h->va[rank]), 0, h->bytes) != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess)
@@ -435,7 +440,9 @@ int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t byte
           }
         }
         if (!ch.agree_min(step_ok, all, err)) return fail(AAR_ECUDA, err);
-        if (!all) {
+        if (!all && h->mc_va != 0) {  // some other rank could not map it: nobody uses it
+          d.MemUnmap(h->mc_va, h->bytes);
+          d.MemAddressFree(h->mc_va, h->bytes);
           h->has_mc = false;
           h->mc_va = 0;
         }
@@ -475,6 +482,7 @@ int aar_heap_create(AarHeap** out, int rank, int world, int device, int64_t byte
       if (!ch.agree_min(1, done, err)) return fail(AAR_ECUDA, err);
     }
   }
+  cleanup.h = nullptr;
   *out = h;
   return AAR_OK;
 }
