@@ -1,0 +1,263 @@
+"""Exhaustive interleaving check of the device flag protocol (race detection without a sanitizer).
+
+The reference needs no race detector: an actor handles one message at a time (SURVEY.md 5.2,
+AllreduceWorker.scala:33).  The device path does have real cross-GPU races to get right — flags versus data,
+ring-slot recycling, ranks more than a round apart — and `compute-sanitizer` cannot see across GPUs (nor is it
+available on the pool this was developed on).  So the PROTOCOL is checked here as a small explicit-state
+model: every rank runs the step sequence of `csrc/cuda/fused_allreduce.cu` (two-shot) or of the one-shot
+kernel, memory is the symmetric region's flag and data words, and a breadth-first search visits every
+interleaving of the ranks' steps for a few ranks, slots and rounds.
+
+What a step is.  Stores to different peers are separate steps where a peer can observe the difference (flags,
+`done` words); the data stores of a phase are one step (no guard ever looks at data, and one location's hazard
+is independent of the others).  A wait is split in two: the step that OBSERVES the flags and fixes the
+contributor set, and the later step that READS the data — the window a recycled slot could be overwritten in.
+Data words carry the tag of the round that wrote them; a read of a word whose tag is not the reader's is the
+violation the search looks for.  With `timeouts=True` every wait may also give up with whatever it has (the
+kernel's timeout / force flag / a dead peer), which is what lets ranks drift more than one round apart.
+
+Checked properties:
+  * safety   — no reader ever consumes a word written for another round (slot recycled too early, flag
+               overtaking data at protocol level, stale flag taken for a fresh one);
+  * liveness — without timeouts no reachable state is stuck before every rank finished every round;
+  * exactness — with all thresholds 1 and no timeouts every reduce and every completion sees all P ranks.
+
+`tests/test_protocol_model.py` runs the configurations the engine actually uses and two seeded bugs (no
+back-pressure; one-shot without gate and with a one-slot ring) that the search must find.
+"""
+from __future__ import annotations
+
+from collections import deque
+from dataclasses import dataclass
+
+# program counters
+GATE, MASK, SDATA, SFLAG, RWAIT, RREAD, BDATA, BFLAG, CWAIT, CREAD, DONE, END = range(12)
+_NAMES = ["gate", "dest-mask", "scatter-data", "scatter-flag", "reduce-wait", "reduce-read", "bcast-data",
+          "bcast-flag", "complete-wait", "complete-read", "done-flag", "end"]
+
+
+@dataclass(frozen=True)
+class ModelConfig:
+    P: int = 2                 # ranks
+    L: int = 2                 # ring slots (maxLag + 1)
+    rounds: int = 3
+    req_reduce: int = 0        # 0 = P
+    req_complete: int = 0      # 0 = P (one reduced chunk per owner in the model)
+    gate_count: int = 0        # thAllreduce gate: peers that must have finished round r-1; 0 = no gate
+    timeouts: bool = False     # any wait may give up with what it has
+    giveups: int = -1          # with timeouts: at most this many give-ups in one execution (-1 = unbounded);
+                               # bounds the search for 3+ ranks, where the unbounded one does not fit in memory
+    oneshot: bool = False      # the one-shot kernel's step sequence instead of the two-shot's
+    backpressure: bool = True  # False = seeded bug: push into a peer's slot without looking at its `done`
+    oneshot_backpressure: bool = False  # the one-shot kernel as it is has NO destination mask;
+                                        # True models the planned fix (same `done + L >= tag` rule as two-shot)
+
+
+@dataclass
+class Result:
+    ok: bool
+    states: int
+    violation: str | None = None
+    trace: list | None = None
+
+
+class _Layout:
+    """Flat indices into the memory tuple: done[q][s], then arr/scat/rfl/sink[q][l][s]."""
+
+    def __init__(self, P: int, L: int):
+        self.P, self.L = P, L
+        self.o_done = 0
+        self.o_arr = P * P
+        self.o_scat = self.o_arr + P * L * P
+        self.o_rfl = self.o_scat + P * L * P
+        self.o_sink = self.o_rfl + P * L * P
+        self.size = self.o_sink + P * L * P
+
+    def done(self, q, s):
+        return self.o_done + q * self.P + s
+
+    def arr(self, q, l, s):
+        return self.o_arr + (q * self.L + l) * self.P + s
+
+    def scat(self, q, l, s):
+        return self.o_scat + (q * self.L + l) * self.P + s
+
+    def rfl(self, q, l, s):
+        return self.o_rfl + (q * self.L + l) * self.P + s
+
+    def sink(self, q, l, s):
+        return self.o_sink + (q * self.L + l) * self.P + s
+
+
+def _put(mem: tuple, writes) -> tuple:
+    m = list(mem)
+    for k, v in writes:
+        m[k] = v
+    return tuple(m)
+
+
+def check(cfg: ModelConfig, max_states: int = 3_000_000) -> Result:
+    P, L, T = cfg.P, cfg.L, cfg.rounds
+    req_r = cfg.req_reduce or P
+    req_c = cfg.req_complete or P
+    lay = _Layout(P, L)
+    full = (1 << P) - 1
+    exact = req_r == P and req_c == P and not cfg.timeouts
+
+    # rank state: (tag, pc, i, ok_mask, mask)
+    init = (tuple((1, GATE, 0, 0, 0) for _ in range(P)), tuple([0] * lay.size), cfg.giveups if cfg.timeouts else 0)
+    parent = {init: None}
+    queue = deque([init])
+
+    def trace_of(state, last):
+        out = [last]
+        while parent[state] is not None:
+            state, what = parent[state]
+            out.append(what)
+        return list(reversed(out))
+
+    def successors(state):
+        """Yields (label, next_state) or (label, None, violation)."""
+        ranks, mem, left = state
+        may_give_up = cfg.timeouts and left != 0
+        for q in range(P):
+            t, pc, i, ok, m = ranks[q]
+            if pc == END:
+                continue
+            l = (t - 1) % L
+            label = f"r{q} t{t} {_NAMES[pc]}" + (f"[{(q + i) % P}]" if pc in (SFLAG, BFLAG, DONE) else "")
+
+            def go(new_rank, writes=(), label=label, gave_up=False):
+                nr = ranks[:q] + (new_rank,) + ranks[q + 1:]
+                if gave_up:
+                    label += " (gave up)"
+                return (label, (nr, _put(mem, writes) if writes else mem, left - 1 if gave_up and left > 0 else left))
+
+            if pc == GATE:
+                have = sum(1 for s in range(P) if s == q or mem[lay.done(q, s)] + 1 >= t)
+                opened = cfg.gate_count <= 0 or t <= 1 or have >= cfg.gate_count
+                if opened or may_give_up:
+                    yield go((t, MASK, 0, 0, 0), gave_up=not opened)
+            elif pc == MASK:
+                if (cfg.oneshot and not cfg.oneshot_backpressure) or not cfg.backpressure:
+                    okm = full   # the one-shot kernel has no destination mask
+                else:
+                    okm = 0
+                    for d in range(P):
+                        if d == q or mem[lay.done(q, d)] + L >= t:
+                            okm |= 1 << d
+                yield go((t, SDATA, 0, okm, 0))
+            elif pc == SDATA:
+                # two-shot: my slice for owner d into d's scat row [me]; one-shot: my whole message, same rows
+                writes = [(lay.scat(d, l, q), t) for d in range(P) if (ok >> d) & 1]
+                yield go((t, SFLAG, 0, ok, 0), writes)
+            elif pc == SFLAG:
+                d = (q + i) % P
+                writes = [(lay.arr(d, l, q), t)] if (ok >> d) & 1 else []
+                nxt = (t, SFLAG, i + 1, ok, 0) if i + 1 < P else (t, RWAIT, 0, ok, 0)
+                yield go(nxt, writes)
+            elif pc == RWAIT:
+                have = 0
+                for s in range(P):
+                    if mem[lay.arr(q, l, s)] == t:
+                        have |= 1 << s
+                met = bin(have).count("1") >= req_r
+                if met or may_give_up:
+                    yield go((t, RREAD, 0, ok, have), gave_up=not met)
+            elif pc == RREAD:
+                for s in range(P):
+                    if (m >> s) & 1 and mem[lay.scat(q, l, s)] != t:
+                        yield (label, None, f"rank {q} round-tag {t}: contribution of rank {s} in slot {l} carries "
+                                            f"tag {mem[lay.scat(q, l, s)]}")
+                        return
+                if exact and m != full:
+                    yield (label, None, f"rank {q} round-tag {t}: reduced {m:b} instead of all ranks")
+                    return
+                if cfg.oneshot:   # one-shot: the local sum IS the result; nothing to broadcast or wait for
+                    yield go((t, DONE, 0, ok, m))
+                else:
+                    yield go((t, BDATA, 0, ok, m))
+            elif pc == BDATA:
+                # a skipped peer's copy is redirected to my own sink row (it is never flagged there)
+                writes = [(lay.sink(d if (ok >> d) & 1 else q, l, q), t) for d in range(P)]
+                yield go((t, BFLAG, 0, ok, m), writes)
+            elif pc == BFLAG:
+                d = (q + i) % P
+                writes = [(lay.rfl(d, l, q), t)] if (ok >> d) & 1 else []
+                nxt = (t, BFLAG, i + 1, ok, m) if i + 1 < P else (t, CWAIT, 0, ok, 0)
+                yield go(nxt, writes)
+            elif pc == CWAIT:
+                have = 0
+                for o in range(P):
+                    if mem[lay.rfl(q, l, o)] == t:
+                        have |= 1 << o
+                met = bin(have).count("1") >= req_c
+                if met or may_give_up:
+                    yield go((t, CREAD, 0, ok, have), gave_up=not met)
+            elif pc == CREAD:
+                for o in range(P):
+                    if (m >> o) & 1 and mem[lay.sink(q, l, o)] != t:
+                        yield (label, None, f"rank {q} round-tag {t}: reduced block of owner {o} in slot {l} "
+                                            f"carries tag {mem[lay.sink(q, l, o)]}")
+                        return
+                if exact and m != full:
+                    yield (label, None, f"rank {q} round-tag {t}: completed with {m:b} instead of all owners")
+                    return
+                yield go((t, DONE, 0, ok, 0))
+            elif pc == DONE:
+                d = (q + i) % P
+                writes = [(lay.done(d, q), t)]
+                if i + 1 < P:
+                    yield go((t, DONE, i + 1, ok, 0), writes)
+                elif t < T:
+                    yield go((t + 1, GATE, 0, 0, 0), writes)
+                else:
+                    yield go((t, END, 0, 0, 0), writes)
+
+    states = 0
+    while queue:
+        state = queue.popleft()
+        states += 1
+        if states > max_states:
+            return Result(False, states, f"state limit {max_states} reached (search incomplete)")
+        moved = False
+        for nxt in successors(state):
+            moved = True
+            if nxt[1] is None:
+                return Result(False, states, nxt[2], trace_of(state, nxt[0]))
+            label, ns = nxt
+            if ns not in parent:
+                parent[ns] = (state, label)
+                queue.append(ns)
+        if not moved and any(r[1] != END for r in state[0]) and not (cfg.timeouts and state[2] == 0):
+            where = ", ".join(f"r{q}: tag {r[0]} at {_NAMES[r[1]]}" for q, r in enumerate(state[0]))
+            return Result(False, states, "stuck (no rank can move): " + where, trace_of(state, "stuck"))
+    return Result(True, states)
+
+
+if __name__ == "__main__":
+    import argparse
+    import time
+
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("-P", type=int, default=2)
+    ap.add_argument("-L", type=int, default=2)
+    ap.add_argument("--rounds", type=int, default=3)
+    ap.add_argument("--req-reduce", type=int, default=0)
+    ap.add_argument("--req-complete", type=int, default=0)
+    ap.add_argument("--gate", type=int, default=0)
+    ap.add_argument("--timeouts", action="store_true")
+    ap.add_argument("--giveups", type=int, default=-1)
+    ap.add_argument("--oneshot", action="store_true")
+    ap.add_argument("--no-backpressure", action="store_true")
+    ap.add_argument("--oneshot-backpressure", action="store_true")
+    a = ap.parse_args()
+    cfg = ModelConfig(a.P, a.L, a.rounds, a.req_reduce, a.req_complete, a.gate, a.timeouts, a.giveups, a.oneshot,
+                      not a.no_backpressure, a.oneshot_backpressure)
+    t0 = time.time()
+    r = check(cfg)
+    print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")
+    if not r.ok:
+        print("  " + r.violation)
+        for step in (r.trace or [])[-40:]:
+            print("    " + step)

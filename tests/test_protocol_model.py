@@ -1,0 +1,67 @@
+"""Race detection for the device protocol: every interleaving of a small model of the flag
+protocol is searched for a reader consuming a recycled slot, a stuck state, or an incomplete sum.  The model
+and what one step stands for: akka_allreduce_b200/utils/protocol_model.py."""
+import pytest
+
+from akka_allreduce_b200.utils.protocol_model import ModelConfig, check
+
+
+@pytest.mark.parametrize("cfg", [
+    ModelConfig(P=2, L=2, rounds=4),                       # flagship: thresholds 1, maxLag 1, gate elided (implied)
+    ModelConfig(P=3, L=2, rounds=3),
+    ModelConfig(P=2, L=1, rounds=4, gate_count=2),         # maxLag 0: one slot, the gate is what keeps it safe
+    ModelConfig(P=3, L=1, rounds=2, gate_count=3),
+    ModelConfig(P=2, L=3, rounds=5),
+], ids=str)
+def test_full_thresholds_are_safe_live_and_exact(cfg):
+    r = check(cfg)
+    assert r.ok, f"{r.violation}\n" + "\n".join(r.trace or [])
+
+
+def test_one_slot_without_gate_gets_stuck():
+    """Why RoundLauncher.gate_implied asks for maxLag >= 1: with a single slot and no gate a fast rank finds the
+    slot of a slower peer still occupied, skips it (back-pressure), and the peer then waits for data that is
+    never sent.  Safe, but not live without timeouts."""
+    r = check(ModelConfig(P=2, L=1, rounds=3))
+    assert not r.ok and r.violation.startswith("stuck")
+
+
+@pytest.mark.parametrize("cfg", [
+    ModelConfig(P=2, L=2, rounds=5, timeouts=True),                                            # timeouts only
+    ModelConfig(P=2, L=2, rounds=5, req_reduce=1, req_complete=1, gate_count=1, timeouts=True),  # thresholds 0.5
+    ModelConfig(P=2, L=3, rounds=5, req_reduce=1, req_complete=1, timeouts=True),                # no gate at all
+    ModelConfig(P=2, L=1, rounds=4, req_reduce=1, req_complete=1, gate_count=1, timeouts=True),
+    ModelConfig(P=3, L=2, rounds=2, req_reduce=2, req_complete=2, gate_count=2, timeouts=True, giveups=2),
+], ids=str)
+def test_partial_thresholds_and_timeouts_never_read_a_recycled_slot(cfg):
+    """Ranks may now be any number of rounds apart (a wait can give up at any point, which also covers a peer
+    that died): back-pressure on `done` is what keeps a reader's slot from being overwritten."""
+    r = check(cfg)
+    assert r.ok, f"{r.violation}\n" + "\n".join(r.trace or [])
+
+
+def test_search_finds_the_seeded_bug():
+    """Same configuration with the back-pressure test removed: the search must come back with the overwrite."""
+    r = check(ModelConfig(P=2, L=2, rounds=4, req_reduce=1, req_complete=1, gate_count=1, timeouts=True,
+                          backpressure=False))
+    assert not r.ok and "carries tag" in r.violation and r.trace
+
+
+def test_oneshot_rules():
+    assert check(ModelConfig(P=2, L=2, rounds=4, oneshot=True)).ok
+    assert check(ModelConfig(P=3, L=2, rounds=3, oneshot=True)).ok
+    assert check(ModelConfig(P=2, L=1, rounds=4, oneshot=True, gate_count=2)).ok
+    # one slot and no gate: a peer overwrites a copy that is still being summed; aar_allreduce_round()
+    # refuses this combination (AAR_EINVAL "one-shot needs maxLag >= 1 or the thAllreduce gate")
+    r = check(ModelConfig(P=2, L=1, rounds=3, oneshot=True))
+    assert not r.ok and "carries tag" in r.violation
+
+
+def test_oneshot_known_gap_under_timeouts_and_its_fix():
+    """Found by this search, documented in DESIGN.md 7: the one-shot kernel has no destination mask, so a rank
+    that gives up two rounds in a row (>= 2 timeouts, 4 s by default) can overwrite a copy a stalled peer is
+    still summing.  Modelled with the two-shot kernel's `done + L >= tag` rule the violation is gone."""
+    r = check(ModelConfig(P=2, L=2, rounds=4, oneshot=True, timeouts=True))
+    assert not r.ok and "carries tag" in r.violation
+    assert sum("gave up" in s for s in r.trace) >= 2
+    assert check(ModelConfig(P=2, L=2, rounds=5, oneshot=True, timeouts=True, oneshot_backpressure=True)).ok
