@@ -2,7 +2,6 @@
 import os
 import subprocess
 import sys
-import threading
 import time
 
 import numpy as np

@@ -2,7 +2,6 @@
 mirror, and the Python geometry mirror agrees with the C++ layout/threshold code."""
 import ctypes as C
 
-import numpy as np
 import pytest
 
 from akka_allreduce_b200 import host

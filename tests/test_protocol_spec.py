@@ -5,7 +5,6 @@ replayed here with the same parameters and the same expected message sequence; l
 the docstrings point at the scenario being reproduced.
 """
 import numpy as np
-import pytest
 
 from akka_allreduce_b200 import host as h
 from harness import Harness, basic_source
