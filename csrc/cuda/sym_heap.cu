@@ -174,15 +174,6 @@ class SideChannel {
     err = "sendmsg to rank " + std::to_string(peer) + ": " + strerror(errno);
     return false;
   }
-  bool recv_one(Packet& pk, int& got_fd, std::string& err) {
-    if (!stash_.empty()) {
-      pk = stash_.back().first;
-      got_fd = stash_.back().second;
-      stash_.pop_back();
-      return true;
-    }
-    return recv_raw(pk, got_fd, err);
-  }
   // Receives until a packet of `kind` (and epoch, for kind 3) shows up; others are stashed.
   bool recv_kind(int kind, int epoch, Packet& pk, int& got_fd, std::string& err) {
     for (size_t i = 0; i < stash_.size(); ++i) {

@@ -591,7 +591,7 @@ void WorkerNode::deliver(const Message& m) {
 
 void WorkerNode::on_local(const Message& m) { deliver(m); }
 
-void WorkerNode::on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) {
+void WorkerNode::on_frame(int /*conn_id*/, Frame kind, const uint8_t* p, size_t n) {
   Reader r{p, n};
   switch (kind) {
     case Frame::Init: {

@@ -74,9 +74,9 @@ class TcpNode : public Mailer {
 
   // --- called on the IO thread ---
   virtual void on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) = 0;
-  virtual void on_closed(int conn_id) {}
+  virtual void on_closed(int /*conn_id*/) {}
   virtual void on_tick() {}
-  virtual void on_local(const Message& m) {}  // message an engine sent to itself
+  virtual void on_local(const Message& /*m*/) {}  // message an engine sent to itself
 
   int connect_to(const PeerAddress& a, int retries = 0);  // returns conn id (blocking connect)
   void queue_frame(int conn_id, Frame kind, const std::vector<uint8_t>& payload);  // any thread
