@@ -95,8 +95,22 @@ def _run(cmd: list[str]) -> None:
         sys.stderr.write(proc.stderr)
 
 
+def host_sanitizer() -> str:
+    """``AAR_HOST_SANITIZE=address|undefined|thread`` builds (and loads) an instrumented copy of the host library
+    in its own directory, next to the normal one; see scripts/sanitize_host.sh."""
+    san = os.environ.get("AAR_HOST_SANITIZE", "").strip().lower()
+    if san and san not in ("address", "undefined", "thread"):
+        raise RuntimeError(f"AAR_HOST_SANITIZE={san!r}: expected address, undefined or thread")
+    return san
+
+
+def host_native_dir() -> Path:
+    san = host_sanitizer()
+    return PKG / f"_native_{san}" if san else NATIVE
+
+
 def host_library_path() -> Path:
-    return NATIVE / ("_aar_host" + sysconfig.get_config_var("EXT_SUFFIX"))
+    return host_native_dir() / ("_aar_host" + sysconfig.get_config_var("EXT_SUFFIX"))
 
 
 def cuda_library_path() -> Path:
@@ -114,10 +128,14 @@ def build_host(force: bool = False) -> Path:
     with _BuildLock():
         if not force and not _stale(out, deps):  # somebody else built it while we waited
             return out
-        objdir = ROOT / "build" / "host"
+        san = host_sanitizer()
+        objdir = ROOT / "build" / ("host_" + san if san else "host")
         objdir.mkdir(parents=True, exist_ok=True)
+        out.parent.mkdir(exist_ok=True)
+        (out.parent / "__init__.py").touch()
+        opt = ["-O1", "-g", "-fno-omit-frame-pointer", f"-fsanitize={san}"] if san else ["-O2"]
         common = [
-            "g++", "-std=c++17", "-O2", "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-parameter",
+            "g++", "-std=c++17", *opt, "-fPIC", "-fvisibility=hidden", "-Wall", "-Wno-unused-parameter",
             f"-I{INCLUDE}", f"-I{CSRC / 'host'}", f"-I{pybind11.get_include()}",
             f"-I{sysconfig.get_paths()['include']}",
         ]
@@ -133,7 +151,8 @@ def build_host(force: bool = False) -> Path:
                 sys.stderr.write(log)
                 raise RuntimeError(f"native build failed compiling {s}")
         tmp = out.with_suffix(".tmp%d" % os.getpid())
-        _run(["g++", "-shared", "-o", str(tmp)] + [str(o) for o in objs] + ["-lpthread"])
+        _run(["g++", "-shared", "-o", str(tmp)] + ([f"-fsanitize={san}"] if san else []) + [str(o) for o in objs] +
+             ["-lpthread"])
         os.replace(tmp, out)
         _record(out, deps)
     return out

@@ -11,7 +11,7 @@ from . import build as _build
 
 def _load():
     _build.build_host()
-    return importlib.import_module("akka_allreduce_b200._native._aar_host")
+    return importlib.import_module(f"akka_allreduce_b200.{_build.host_native_dir().name}._aar_host")
 
 
 _lib = _load()

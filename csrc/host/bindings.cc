@@ -252,23 +252,26 @@ PYBIND11_MODULE(_aar_host, m) {
       .def("add_probe", [](PyBus& b) { return b.bus.add_probe(); })
       .def(
           "add_worker",
-          [](PyBus& b, py::object source, py::object sink, WorkerOptions opts) {
+          [](py::object self, py::object source, py::object sink, WorkerOptions opts) {
+            PyBus& b = self.cast<PyBus&>();
             const Endpoint ep = b.bus.add_endpoint(nullptr);
             b.workers.push_back(
                 std::make_unique<WorkerEngine>(ep, wrap_source(source), wrap_sink(sink), &b.bus, opts));
             WorkerEngine* w = b.workers.back().get();
             b.bus.rebind(ep, [w](const Message& msg) { w->handle(msg); });
-            return py::make_tuple(ep, py::cast(w, py::return_value_policy::reference));
+            // the bus owns the engine (and is its mailer): the handle keeps the bus alive, not the other way round
+            return py::make_tuple(ep, py::cast(w, py::return_value_policy::reference_internal, self));
           },
           py::arg("source"), py::arg("sink"), py::arg("options") = WorkerOptions{})
       .def(
           "add_master",
-          [](PyBus& b, MasterConfig cfg, bool verbose) {
+          [](py::object self, MasterConfig cfg, bool verbose) {
+            PyBus& b = self.cast<PyBus&>();
             const Endpoint ep = b.bus.add_endpoint(nullptr);
             b.masters.push_back(std::make_unique<MasterEngine>(ep, cfg, &b.bus, verbose));
             MasterEngine* me = b.masters.back().get();
             b.bus.rebind(ep, [me](const Message& msg) { me->handle(msg); });
-            return py::make_tuple(ep, py::cast(me, py::return_value_policy::reference));
+            return py::make_tuple(ep, py::cast(me, py::return_value_policy::reference_internal, self));
           },
           py::arg("config"), py::arg("verbose") = false)
       .def("send", [](PyBus& b, Endpoint to, Message msg) { b.bus.send(to, std::move(msg)); })
