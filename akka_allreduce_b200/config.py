@@ -174,6 +174,8 @@ def parse_hocon(text: str) -> dict:
 
     def value():
         nonlocal i
+        if i >= len(toks):
+            raise ValueError("config: unexpected end of input (a key without a value?)")
         kind, tok = toks[i]
         if (kind, tok) == ("p", "{"):
             i += 1
@@ -181,13 +183,19 @@ def parse_hocon(text: str) -> dict:
         if (kind, tok) == ("p", "["):
             i += 1
             out = []
-            while toks[i] != ("p", "]"):
+            while True:
+                if i >= len(toks):
+                    raise ValueError("config: missing ']'")
+                if toks[i] == ("p", "]"):
+                    break
                 if toks[i] == ("p", ","):
                     i += 1
                     continue
                 out.append(value())
             i += 1
             return out
+        if kind == "p":
+            raise ValueError(f"config: expected a value, found {tok!r}")
         i += 1
         return tok if kind == "s" else _scalar(tok)
 

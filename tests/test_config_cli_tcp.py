@@ -20,6 +20,24 @@ def test_hocon_subset():
     assert t == {"a": {"b": 1, "c": "x y", "d": 2.5}, "e": [1, 2], "f": {"g": {"h": 10.0}}, "i": False}
 
 
+def test_hocon_parser_rejects_garbage_with_valueerror_only():
+    """Any text either parses or raises ValueError (a config typo must not surface as an IndexError)."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=400, deadline=None)
+    @given(st.text(alphabet='ab.= :{}[],"#/\n 19smh-', max_size=24))
+    def run(text):
+        try:
+            assert isinstance(parse_hocon(text), dict)
+        except ValueError:
+            pass
+
+    run()
+    for broken in ("a =", "a = [1, 2", "a { b = 1", "}", "a = ]"):
+        with pytest.raises(ValueError):
+            parse_hocon(broken)
+
+
 def test_default_config_file_matches_reference_hardcoded_values():
     """AllreduceMaster.scala:98-107: maxLag 1, maxRound 100, th 1/1/0.8, 2 workers, dataSize 10, chunk 2."""
     c = load_config(DEFAULT_CONFIG_PATH)
