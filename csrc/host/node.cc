@@ -40,6 +40,10 @@ struct Writer {
   }
 };
 
+// Largest frame a node accepts: a chunk of 2^28 floats plus its header.  (Akka remoting, which the
+// reference runs on, has the same kind of limit: maximum-frame-size, 128 kB unless configured.)
+constexpr uint32_t kMaxFrameBytes = (1u << 30) + 64;
+
 struct Reader {
   const uint8_t* p;
   size_t n;
@@ -266,6 +270,10 @@ bool TcpNode::pump_reads(int id, Conn& c) {
   while (c.in.size() - off >= 5) {
     uint32_t n;
     std::memcpy(&n, c.in.data() + off, 4);
+    if (n > kMaxFrameBytes) {  // not one of ours (or corrupt): do not buffer gigabytes waiting for it
+      std::fprintf(stderr, "[aar node] frame of %u bytes announced on connection %d: closing it\n", n, id);
+      return false;
+    }
     if (c.in.size() - off < 5 + static_cast<size_t>(n)) break;
     const Frame kind = static_cast<Frame>(c.in[off + 4]);
     try {

@@ -115,6 +115,49 @@ def test_tcp_cluster_python_callbacks():
             assert (d == P * (np.arange(n, dtype=np.float32) + it)).all() and (c == P).all()
 
 
+def test_coordinator_survives_garbage_on_its_port():
+    """Something that is not a worker connects to the coordinator port: an absurd frame length gets the connection
+    closed, undecodable frames are dropped, and a normal job on the same coordinator still runs to the end."""
+    import socket
+    import struct
+
+    P, n = 2, 12
+    cfg = _cluster(P, n, 4, 10)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    junk = []
+    try:
+        s1 = socket.create_connection(("127.0.0.1", port), timeout=5)
+        s1.sendall(struct.pack("<IB", 0xFFFFFFF0, 2) + b"x" * 64)          # 4 GB frame announced
+        s2 = socket.create_connection(("127.0.0.1", port), timeout=5)
+        for kind in range(0, 12):                                             # every frame kind, truncated payloads
+            s2.sendall(struct.pack("<IB", 3, kind) + b"\x01\x02\x03")
+        s2.sendall(os.urandom(4096))
+        junk = [s1, s2]
+        s1.settimeout(5)
+        assert s1.recv(1) == b""                                              # the coordinator hung up on s1
+        outs = [dict() for _ in range(P)]
+        workers = []
+        for i in range(P):
+            def source(req):
+                return AllReduceInput(np.ones(n, dtype=np.float32))
+
+            def sink(out, i=i):
+                outs[i][out.iteration] = np.array(out.data)
+
+            w = AllreduceWorker(source, sink, master_port=port)
+            w.start()
+            workers.append(w)
+        assert master.wait(30.0), f"master stuck at round {master.round}"
+        for w in workers:
+            w.stop()
+    finally:
+        for s in junk:
+            s.close()
+        master.stop()
+    assert all(sorted(o) == list(range(11)) and all((d == P).all() for d in o.values()) for o in outs)
+
+
 def test_tcp_cluster_survives_dead_worker_with_thresholds():
     """Failure path (AllreduceMaster.scala:46-52): one of 4 workers dies; thresholds 0.75 keep rounds going
     and the master drops it from the set."""
