@@ -58,6 +58,8 @@ def _stale(target: Path, deps: list[Path], extra: str = "") -> bool:
     """A library is stale when the digest of its sources differs from the one recorded at build time.
     (Content, not mtimes: a snapshot copied to another machine keeps its libraries.)"""
     stamp = target.with_suffix(target.suffix + ".srchash")
+    if target.exists() and not CSRC.exists():
+        return False  # installed package: the libraries were built at install time, there is nothing to rebuild from
     if not target.exists() or not stamp.exists():
         return True
     return stamp.read_text().strip() != _digest(deps, extra)
