@@ -49,6 +49,8 @@ class ModelConfig:
                                # bounds the search for 3+ ranks, where the unbounded one does not fit in memory
     oneshot: bool = False      # the one-shot kernel's step sequence instead of the two-shot's
     backpressure: bool = True  # False = seeded bug: push into a peer's slot without looking at its `done`
+    early_write: bool = False  # zero-copy input (`input_view`): the caller fills the round's staging rows BEFORE the
+                               # launch, i.e. before the gate and without the destination mask
     oneshot_backpressure: bool = False  # the one-shot kernel as it is has NO destination mask;
                                         # True models the planned fix (same `done + L >= tag` rule as two-shot)
 
@@ -133,7 +135,10 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000) -> Result:
                     label += " (gave up)"
                 return (label, (nr, _put(mem, writes) if writes else mem, left - 1 if gave_up and left > 0 else left))
 
-            if pc == GATE:
+            if pc == GATE and cfg.early_write and i == 0:
+                # the source callback has produced round t's message straight into the staging slot
+                yield go((t, GATE, 1, 0, 0), [(lay.scat(d, l, q), t) for d in range(P)], label=label + " (caller fills staging)")
+            elif pc == GATE:
                 have = sum(1 for s in range(P) if s == q or mem[lay.done(q, s)] + 1 >= t)
                 opened = cfg.gate_count <= 0 or t <= 1 or have >= cfg.gate_count
                 if opened or may_give_up:
@@ -149,7 +154,7 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000) -> Result:
                 yield go((t, SDATA, 0, okm, 0))
             elif pc == SDATA:
                 # two-shot: my slice for owner d into d's scat row [me]; one-shot: my whole message, same rows
-                writes = [(lay.scat(d, l, q), t) for d in range(P) if (ok >> d) & 1]
+                writes = [] if cfg.early_write else [(lay.scat(d, l, q), t) for d in range(P) if (ok >> d) & 1]
                 yield go((t, SFLAG, 0, ok, 0), writes)
             elif pc == SFLAG:
                 d = (q + i) % P
@@ -251,9 +256,10 @@ if __name__ == "__main__":
     ap.add_argument("--oneshot", action="store_true")
     ap.add_argument("--no-backpressure", action="store_true")
     ap.add_argument("--oneshot-backpressure", action="store_true")
+    ap.add_argument("--early-write", action="store_true")
     a = ap.parse_args()
     cfg = ModelConfig(a.P, a.L, a.rounds, a.req_reduce, a.req_complete, a.gate, a.timeouts, a.giveups, a.oneshot,
-                      not a.no_backpressure, a.oneshot_backpressure)
+                      not a.no_backpressure, a.early_write, a.oneshot_backpressure)
     t0 = time.time()
     r = check(cfg)
     print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")

@@ -65,3 +65,16 @@ def test_oneshot_known_gap_under_timeouts_and_its_fix():
     assert not r.ok and "carries tag" in r.violation
     assert sum("gave up" in s for s in r.trace) >= 2
     assert check(ModelConfig(P=2, L=2, rounds=5, oneshot=True, timeouts=True, oneshot_backpressure=True)).ok
+
+
+def test_zero_copy_input_preconditions():
+    """`DeviceAllreduce.input_view` lets the caller write a round's message straight into the staging slot, before
+    the launch and therefore before the gate and the destination mask.  It is only handed out in NVLS mode, which
+    needs thReduce = 1: then nobody can reduce round r+1 before every rank has finished reading round r, whatever
+    thComplete is.  Below thReduce = 1, or once waits may time out, the early write can hit a slot a slow peer is
+    still reading (same 2-timeouts corner as the one-shot gap)."""
+    assert check(ModelConfig(P=2, L=2, rounds=4, early_write=True)).ok
+    assert check(ModelConfig(P=3, L=2, rounds=3, early_write=True, req_complete=2)).ok
+    assert check(ModelConfig(P=2, L=1, rounds=4, early_write=True, gate_count=2)).ok
+    assert not check(ModelConfig(P=2, L=3, rounds=5, early_write=True, req_reduce=1, req_complete=1)).ok
+    assert not check(ModelConfig(P=2, L=2, rounds=4, early_write=True, timeouts=True)).ok
