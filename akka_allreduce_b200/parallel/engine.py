@@ -139,10 +139,13 @@ class DeviceAllreduce:
     def output_view(self, round_: int) -> torch.Tensor | None:
         """Tensor aliasing the sink slot of ``round_``: the reduced message lands here anyway, so using it
         as ``out`` skips the flush copy.  Valid until the slot is recycled ``maxLag + 1`` rounds later.
-        Only handed out when no chunk can be missing (thComplete = 1): a straggler's late push could
-        otherwise overwrite zeros the caller was told about."""
+        Only handed out when both data thresholds are 1.  Below thComplete = 1 a straggler's late push could
+        overwrite zeros the caller was told about; below thReduce = 1 the owners can reduce round r + maxLag + 1
+        WITHOUT this rank and write its sink slot while the caller is still reading round r from it (with
+        thReduce = 1 they cannot start before this rank has scattered that round, i.e. given the slot back).
+        Found by the protocol search: ModelConfig(output_view=True, req_reduce < P)."""
         l, g = self.launcher, self.geo
-        if not self.zero_copy_ok or l.req_complete < g.total_chunks:
+        if not self.zero_copy_ok or l.req_complete < g.total_chunks or l.req_reduce < g.world:
             return None
         esz = torch.empty((), dtype=l.wire_dtype).element_size()
         slot = round_ % g.slots

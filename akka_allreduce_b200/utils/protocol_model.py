@@ -51,6 +51,8 @@ class ModelConfig:
     backpressure: bool = True  # False = seeded bug: push into a peer's slot without looking at its `done`
     early_write: bool = False  # zero-copy input (`input_view`): the caller fills the round's staging rows BEFORE the
                                # launch, i.e. before the gate and without the destination mask
+    output_view: bool = False  # zero-copy output (`output_view`): the caller keeps reading round r's sink slot until it
+                               # launches round r+L (the worker loop delivers sink(r) before that launch)
     oneshot_backpressure: bool = False  # the one-shot kernel as it is has NO destination mask;
                                         # True models the planned fix (same `done + L >= tag` rule as two-shot)
 
@@ -135,6 +137,12 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000) -> Result:
                     label += " (gave up)"
                 return (label, (nr, _put(mem, writes) if writes else mem, left - 1 if gave_up and left > 0 else left))
 
+            if pc == GATE and cfg.output_view and i == 0 and t > L and not cfg.oneshot:
+                bad = [o for o in range(P) if mem[lay.sink(q, l, o)] > t - L]
+                if bad:
+                    yield (label, None, f"rank {q}: output view of round-tag {t - L} (slot {l}) was overwritten by owner "
+                                        f"{bad[0]} for tag {mem[lay.sink(q, l, bad[0])]} before the caller gave the slot back")
+                    return
             if pc == GATE and cfg.early_write and i == 0:
                 # the source callback has produced round t's message straight into the staging slot
                 yield go((t, GATE, 1, 0, 0), [(lay.scat(d, l, q), t) for d in range(P)], label=label + " (caller fills staging)")
@@ -257,9 +265,10 @@ if __name__ == "__main__":
     ap.add_argument("--no-backpressure", action="store_true")
     ap.add_argument("--oneshot-backpressure", action="store_true")
     ap.add_argument("--early-write", action="store_true")
+    ap.add_argument("--output-view", action="store_true")
     a = ap.parse_args()
     cfg = ModelConfig(a.P, a.L, a.rounds, a.req_reduce, a.req_complete, a.gate, a.timeouts, a.giveups, a.oneshot,
-                      not a.no_backpressure, a.early_write, a.oneshot_backpressure)
+                      not a.no_backpressure, a.early_write, a.output_view, a.oneshot_backpressure)
     t0 = time.time()
     r = check(cfg)
     print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")

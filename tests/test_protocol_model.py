@@ -78,3 +78,15 @@ def test_zero_copy_input_preconditions():
     assert check(ModelConfig(P=2, L=1, rounds=4, early_write=True, gate_count=2)).ok
     assert not check(ModelConfig(P=2, L=3, rounds=5, early_write=True, req_reduce=1, req_complete=1)).ok
     assert not check(ModelConfig(P=2, L=2, rounds=4, early_write=True, timeouts=True)).ok
+
+
+def test_zero_copy_output_preconditions():
+    """`DeviceAllreduce.output_view`: the caller reads round r from the sink slot until it launches round r+L.
+    Safe with thReduce = 1 (owners cannot reduce round r+L before this rank has scattered it); with thReduce < 1
+    they can, and overwrite the view — which is why the engine only hands the view out when both thresholds are 1
+    (this search found the missing thReduce condition)."""
+    assert check(ModelConfig(P=2, L=2, rounds=5, output_view=True)).ok
+    assert check(ModelConfig(P=3, L=2, rounds=4, output_view=True)).ok
+    assert check(ModelConfig(P=2, L=1, rounds=4, output_view=True, gate_count=2)).ok
+    r = check(ModelConfig(P=3, L=2, rounds=4, output_view=True, req_reduce=2))
+    assert not r.ok and "output view" in r.violation
