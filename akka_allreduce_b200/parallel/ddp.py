@@ -33,6 +33,7 @@ class AllreduceCommHook:
         self.timeout_ms, self.algo, self.ctas = timeout_ms, algo, ctas
         self.stream = torch.cuda.Stream(device=self.device)
         self._engines: Dict[Tuple[int, torch.dtype], DeviceAllreduce] = {}
+        self._outs: Dict[Tuple[int, torch.dtype], torch.Tensor] = {}  # only used with thresholds below 1
         self.buckets_reduced = 0
         self.kernel_launches = 0
 
@@ -58,7 +59,15 @@ class AllreduceCommHook:
         self.stream.wait_stream(torch.cuda.current_stream(self.device))  # the bucket's gradients are final
         with torch.cuda.stream(self.stream):
             before = eng.launcher.launches
-            eng.allreduce(buf, buf, None, stream=self.stream)  # in place: mean over the contributors
+            if eng.partial_thresholds:
+                # a round that may finish without this rank must not write over gradients still to be scattered
+                out = self._outs.get((buf.numel(), buf.dtype))
+                if out is None:
+                    out = self._outs[(buf.numel(), buf.dtype)] = torch.empty_like(buf)
+                eng.allreduce(buf, out, None, stream=self.stream)
+                buf.copy_(out, non_blocking=True)
+            else:
+                eng.allreduce(buf, buf, None, stream=self.stream)  # in place: mean over the contributors
             self.kernel_launches += eng.launcher.launches - before
             buf.record_stream(self.stream)
             fut.set_result(buf)  # captures the side stream's position
@@ -69,3 +78,4 @@ class AllreduceCommHook:
         for eng in self._engines.values():
             eng.close()
         self._engines.clear()
+        self._outs.clear()

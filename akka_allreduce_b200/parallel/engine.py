@@ -125,6 +125,11 @@ class DeviceAllreduce:
         g, l = self.geo, self.launcher
         return g.step % 128 == 0 and l.dtype == l.wire_dtype and l.scale == 1.0 and self.algo != "oneshot"
 
+    @property
+    def partial_thresholds(self) -> bool:
+        """True when a round may finish without some contribution (thReduce < 1 or thComplete < 1)."""
+        return self.launcher.req_reduce < self.geo.world or self.launcher.req_complete < self.geo.total_chunks
+
     def input_view(self, round_: int) -> torch.Tensor | None:
         """Tensor aliasing the staging slot of ``round_`` (NVLS mode only: there the scatter stages the
         message locally and the switch pulls it).  A source written here needs no copy at all."""
@@ -165,6 +170,13 @@ class DeviceAllreduce:
             raise ValueError(f"Input data size {src.numel()} is different from initialization time {g.n}!")
         if src.dtype != self.launcher.dtype or out.dtype != self.launcher.dtype:
             raise ValueError("dtype differs from the engine's")
+        if self.partial_thresholds and src.data_ptr() < out.data_ptr() + out.numel() * out.element_size() and \
+                out.data_ptr() < src.data_ptr() + src.numel() * src.element_size():
+            # With thresholds of 1 a block of `out` is written only after its owner has received THIS rank's slice
+            # of it, so the launch may run in place.  Below 1 the owner can finish without this rank: the result
+            # (or the zeros of a missing chunk) could land on source elements that are still to be scattered.
+            raise ValueError("allreduce in place (out overlaps src) needs thReduce = thComplete = 1; "
+                             "pass a separate output tensor")
         r = self.round if round_ is None else round_
         a = self._launch
         self.launcher.fill(a, r, inj)

@@ -45,3 +45,26 @@ def test_static_scratch_limit_is_checked_before_any_cuda_call():
     a = K.AarLaunch()
     a.world, a.n, a.max_chunk, a.block_step, a.emu = 8, 1 << 20, 16, 0, 1
     assert K.lib().aar_allreduce_round_static_scratch(C.byref(a), None) == -4
+
+
+def test_in_place_round_is_refused_below_full_thresholds():
+    """The guard sits in front of any CUDA call, so it can be checked without a device: in place is fine with
+    thresholds 1 (a block of `out` is written only after its owner has this rank's slice of it) and refused below."""
+    import types
+
+    import torch
+
+    from akka_allreduce_b200.parallel.engine import DeviceAllreduce
+
+    eng = object.__new__(DeviceAllreduce)
+    eng.geo = types.SimpleNamespace(n=64, world=4, total_chunks=8)
+    eng.launcher = types.SimpleNamespace(dtype=torch.float32, req_reduce=3, req_complete=8)
+    assert eng.partial_thresholds
+    x = torch.zeros(64)
+    with pytest.raises(ValueError, match="in place"):
+        eng.allreduce(x, x)
+    big = torch.zeros(96)
+    with pytest.raises(ValueError, match="in place"):
+        eng.allreduce(big[:64], big[32:])          # partial overlap counts too
+    eng.launcher.req_reduce = 4
+    assert not eng.partial_thresholds
