@@ -142,7 +142,7 @@ class DeviceWorker:
             th_allreduce=cfg.thresholds.thAllreduce if gate_on_device else None,
             device=self.device_index, uds_dir=self.uds_dir or default_uds_dir(self.master_port),
             align_blocks=self.align_blocks, ctas=dev_cfg.ctas or None, timeout_ms=dev_cfg.timeoutMs,
-            scale=dev_cfg.scale, normalize=dev_cfg.normalize)
+            scale=dev_cfg.scale, normalize=dev_cfg.normalize, algo=dev_cfg.algo)
         eng = self.engine
         dev = eng.device
         self.log.info("----Actor id = %d on cuda:%d; peers = %d; thReduce = %s, thComplete = %s, maxLag = %d; "

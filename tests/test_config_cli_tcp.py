@@ -277,3 +277,22 @@ def test_native_cpu_cluster_binary():
     for argv in (["2", "10", "2", "500", "1", "1", "1", "0.8"], ["4", "778", "3", "200", "3", "1", "1", "1"]):
         p = subprocess.run([exe] + argv, capture_output=True, text=True, timeout=120)
         assert p.returncode == 0 and "finished:" in p.stdout and "0 sink assertion failures" in p.stdout, p.stdout + p.stderr
+
+
+def test_every_config_key_is_read_somewhere():
+    """A key that parses but is never consulted is a silent no-op (device.algo was one): every field of every
+    section must be referenced by package code outside config.py."""
+    import dataclasses
+    import re
+
+    from akka_allreduce_b200 import config as c
+
+    pkg = os.path.join(ROOT, "akka_allreduce_b200")
+    text = ""
+    for base, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith(".py") and f != "config.py":
+                text += open(os.path.join(base, f)).read()
+    unused = [f"{sec}.{f.name}" for sec, cls in c._SECTIONS.items() for f in dataclasses.fields(cls)
+              if not re.search(rf"\.{f.name}\b", text)]
+    assert not unused, unused
