@@ -13,10 +13,11 @@ CLI (positional order of the reference, README.md:3)::
 from __future__ import annotations
 
 import argparse
+import os
 import sys
 
 from . import host
-from .config import AllreduceConfig, DataConfig, ThresholdConfig, WorkerConfig, load_config
+from .config import DEFAULT_CONFIG_PATH, AllreduceConfig, DataConfig, ThresholdConfig, WorkerConfig, load_config
 from .utils.logging import get_logger
 
 
@@ -82,7 +83,9 @@ def build_config(argv: list[str]) -> AllreduceConfig:
         ap.add_argument("--" + k, type=int)
     ap.add_argument("--host")
     a = ap.parse_args(argv)
-    cfg = load_config(a.config)
+    # like the reference, whose application.conf is picked up without being named: the checkout's (or the
+    # packaged) application.conf is read unless --config / AAR_CONFIG names another file
+    cfg = load_config(a.config or os.environ.get("AAR_CONFIG") or DEFAULT_CONFIG_PATH)
     if a.numOfWorkers is not None:
         cfg.worker.totalSize = a.numOfWorkers
         if a.dataSize is None and a.config is None:

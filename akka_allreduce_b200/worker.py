@@ -22,13 +22,14 @@ and optionally asserts ``output == input*k`` and ``count == k`` (AllreduceWorker
 from __future__ import annotations
 
 import argparse
+import os
 import sys
 
 import numpy as np
 
 from . import host
 from .api import AllReduceInput, AllReduceInputRequest, AllReduceOutput, DataSink, DataSource
-from .config import AllreduceConfig, load_config
+from .config import DEFAULT_CONFIG_PATH, AllreduceConfig, load_config
 from .utils.logging import get_logger
 
 
@@ -133,7 +134,9 @@ def main(argv: list[str] | None = None) -> int:
     ap.add_argument("--assert-multiple", type=int)
     ap.add_argument("--backend", choices=["cpu", "cuda"])
     a = ap.parse_args(sys.argv[1:] if argv is None else argv)
-    cfg = load_config(a.config)
+    # like the reference, whose application.conf is picked up without being named: the checkout's (or the
+    # packaged) application.conf is read unless --config / AAR_CONFIG names another file
+    cfg = load_config(a.config or os.environ.get("AAR_CONFIG") or DEFAULT_CONFIG_PATH)
     data_size = a.dataSize if a.dataSize is not None else cfg.data.dataSize
     w = start_up(a.port, data_size,
                  a.checkpoint if a.checkpoint is not None else cfg.worker.checkpoint,

@@ -296,3 +296,15 @@ def test_every_config_key_is_read_somewhere():
     unused = [f"{sec}.{f.name}" for sec, cls in c._SECTIONS.items() for f in dataclasses.fields(cls)
               if not re.search(rf"\.{f.name}\b", text)]
     assert not unused, unused
+
+
+def test_cli_reads_the_config_file_without_being_told(tmp_path, monkeypatch):
+    """The reference picks up application.conf on its own; so do the launchers (AAR_CONFIG names another file)."""
+    p = tmp_path / "other.conf"
+    p.write_text("allreduce { worker { totalSize = 5, maxLag = 2 }, thresholds.thComplete = 0.5 }")
+    monkeypatch.setenv("AAR_CONFIG", str(p))
+    c = build_config([])
+    assert (c.worker.totalSize, c.worker.maxLag, c.thresholds.thComplete) == (5, 2, 0.5)
+    assert build_config(["2600", "3"]).worker.totalSize == 3          # the command line still wins
+    monkeypatch.delenv("AAR_CONFIG")
+    assert build_config([]).worker.totalSize == 2                     # conf/application.conf
