@@ -63,3 +63,37 @@ def test_no_loss_long_run_is_exact_for_every_lag():
             assert sorted(o) == list(range(1501))
             for d, cnt in o.values():
                 assert (d == 7.0).all() and (cnt == P).all()
+
+
+def test_engine_survives_malformed_messages():
+    """Wire-level fuzz of one worker engine: ids, chunk numbers, rounds and payload sizes that no peer of this job
+    could send.  Every message is either handled or recorded in `errors` (the reference's tryCatch,
+    AllreduceWorker.scala:287-299); nothing may reach Python as an exception, let alone crash.  The same fuzz was
+    run against the ASan build (profiles/host_sanitizers.md)."""
+    import random
+
+    from harness import Harness
+
+    rng = random.Random(7)
+    recorded = 0
+    for _ in range(120):
+        P, n, mc, lag = rng.randint(1, 5), rng.randint(1, 40), rng.randint(1, 9), rng.randint(0, 3)
+        idx = rng.randrange(P)
+        hs = Harness(size=n)
+        hs.init(hs.peers_as_probe(P, real=idx), P, idx, rng.choice([0.5, 0.7, 1.0]), rng.choice([0.5, 0.8, 1.0]),
+                lag, n, mc)
+        for _ in range(rng.randint(5, 40)):
+            kind, rnd = rng.random(), rng.randint(-2, 8)
+            val = np.asarray([rng.random() for _ in range(rng.randint(0, mc + 3))], dtype=np.float32)
+            src, chunk = rng.randint(-1, P + 1), rng.randint(-1, 12)
+            dest = rng.choice([idx, idx, idx, rng.randint(-1, P + 1)])
+            if kind < 0.2:
+                hs.tell(h.StartAllreduce(rnd))
+            elif kind < 0.6:
+                hs.tell(h.ScatterBlock(val, src, dest, chunk, rnd))
+            elif kind < 0.95:
+                hs.tell(h.ReduceBlock(val, src, dest, chunk, rnd, rng.randint(-1, P + 2)))
+            else:
+                hs.tell(h.CompleteAllreduce(src, rnd))
+        recorded += len(hs.worker.errors)
+    assert recorded > 100          # the fuzz does hit the guarded paths
