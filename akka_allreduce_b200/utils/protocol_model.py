@@ -100,7 +100,11 @@ def _put(mem: tuple, writes) -> tuple:
     return tuple(m)
 
 
-def check(cfg: ModelConfig, max_states: int = 3_000_000) -> Result:
+def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: int = 0,
+          giveup_weight: float = 0.02) -> Result:
+    """Breadth-first search over every interleaving (`walks` = 0), or `walks` random executions for
+    configurations too large to enumerate (8 ranks, tens of rounds); a give-up is then taken with relative
+    weight `giveup_weight` so that runs are mostly normal with the occasional timeout."""
     P, L, T = cfg.P, cfg.L, cfg.rounds
     req_r = cfg.req_reduce or P
     req_c = cfg.req_complete or P
@@ -227,6 +231,35 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000) -> Result:
                 else:
                     yield go((t, END, 0, 0, 0), writes)
 
+    if walks > 0:
+        import random
+
+        rng = random.Random(seed)
+        steps = 0
+        for _ in range(walks):
+            state, path = init, []
+            # uniform scheduling keeps the ranks in lock step; the bugs live in skew, so every execution draws a
+            # speed per rank (log-uniform over three decades) and redraws it now and then
+            speed = [10 ** rng.uniform(-3, 0) for _ in range(P)]
+            while True:
+                nxt = list(successors(state))
+                if not nxt:
+                    if any(r[1] != END for r in state[0]) and not (cfg.timeouts and state[2] == 0):
+                        where = ", ".join(f"r{q}: tag {r[0]} at {_NAMES[r[1]]}" for q, r in enumerate(state[0]))
+                        return Result(False, steps, "stuck (no rank can move): " + where, path + ["stuck"])
+                    break
+                bad = [x for x in nxt if x[1] is None]
+                if bad:
+                    return Result(False, steps, bad[0][2], path + [bad[0][0]])
+                if rng.random() < 0.01:
+                    speed = [10 ** rng.uniform(-3, 0) for _ in range(P)]
+                weights = [(giveup_weight if x[0].endswith("(gave up)") else 1.0) * speed[int(x[0][1:x[0].index(" ")])]
+                           for x in nxt]
+                label, state = rng.choices(nxt, weights)[0]
+                path.append(label)
+                steps += 1
+        return Result(True, steps)
+
     states = 0
     while queue:
         state = queue.popleft()
@@ -266,11 +299,13 @@ if __name__ == "__main__":
     ap.add_argument("--oneshot-backpressure", action="store_true")
     ap.add_argument("--early-write", action="store_true")
     ap.add_argument("--output-view", action="store_true")
+    ap.add_argument("--walks", type=int, default=0, help="random executions instead of the exhaustive search")
+    ap.add_argument("--seed", type=int, default=0)
     a = ap.parse_args()
     cfg = ModelConfig(a.P, a.L, a.rounds, a.req_reduce, a.req_complete, a.gate, a.timeouts, a.giveups, a.oneshot,
                       not a.no_backpressure, a.early_write, a.output_view, a.oneshot_backpressure)
     t0 = time.time()
-    r = check(cfg)
+    r = check(cfg, walks=a.walks, seed=a.seed)
     print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")
     if not r.ok:
         print("  " + r.violation)

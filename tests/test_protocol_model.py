@@ -90,3 +90,14 @@ def test_zero_copy_output_preconditions():
     assert check(ModelConfig(P=2, L=1, rounds=4, output_view=True, gate_count=2)).ok
     r = check(ModelConfig(P=3, L=2, rounds=4, output_view=True, req_reduce=2))
     assert not r.ok and "output view" in r.violation
+
+
+def test_random_executions_at_eight_ranks():
+    """Configurations too large to enumerate: random executions with a random speed per rank (the bugs live in
+    skew).  The 8-rank production shapes pass; the seeded bug is still found."""
+    assert check(ModelConfig(P=8, L=2, rounds=8), walks=20, seed=1).ok
+    assert check(ModelConfig(P=8, L=3, rounds=8, req_reduce=6, req_complete=6, gate_count=6, timeouts=True),
+                 walks=40, seed=2).ok
+    r = check(ModelConfig(P=6, L=2, rounds=10, req_reduce=4, req_complete=4, gate_count=4, timeouts=True,
+                          backpressure=False), walks=300, seed=3)
+    assert not r.ok and "carries tag" in r.violation
