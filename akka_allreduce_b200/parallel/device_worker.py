@@ -28,6 +28,7 @@ import torch
 from .. import host
 from ..api import AllReduceInput, AllReduceInputRequest, AllReduceOutput, DataSink, DataSource
 from ..config import AllreduceConfig
+from ..utils.affinity import bind_to_gpu
 from ..utils.logging import get_logger
 from .engine import DeviceAllreduce, default_uds_dir
 
@@ -134,6 +135,9 @@ class DeviceWorker:
             local = os.environ.get("LOCAL_RANK")
             self.device_index = int(local) if local is not None else self.id % torch.cuda.device_count()
         torch.cuda.set_device(self.device_index)
+        placement = bind_to_gpu(self.device_index)  # this thread and the ones it starts: cores next to the GPU
+        if placement:
+            self.log.info("----bound to NUMA node %d (%d cpus)", placement["numa_node"], placement["cpus"])
         dtype = _DTYPES[dev_cfg.dtype]
         gate_on_device = dev_cfg.gate == "device"
         self.engine = DeviceAllreduce(

@@ -66,6 +66,9 @@ def main() -> int:
             return 2
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # before anything is allocated: run (and first-touch pinned buffers) on the cores next to this GPU
+    from akka_allreduce_b200.utils.affinity import bind_to_gpu
+    placement = bind_to_gpu(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     K.lib()  # fail loudly here if the native library is missing
@@ -205,6 +208,7 @@ def main() -> int:
                        if args.size_mb == 64 else f"allreduce {args.size_mb}MB fp32",
                        "global_batch": world, "seq_len": n, "parallelism": f"dp{world}",
                        "workers": world, "dataSize": n, "maxChunkSize": mc, "maxLag": 1,
+                       "cpu_placement": placement,  # rank 0's; None = left to the OS (single node / hidden sysfs)
                        "l2": (f"working set larger than L2: {L} staging + {L} sink slots + 2 count buffers of {args.size_mb:g} MB"
                               if zero_copy else f"inputs larger than L2: {NSRC} rotating {args.size_mb:g} MB sources")},
             "clocks": {"sm_mhz": clocks.summary["sm_mhz"], "sm_max_mhz": clocks.summary["sm_max_mhz"],

@@ -21,3 +21,44 @@ def test_gpt2_tiny_forward_backward_cpu():
     assert torch.isfinite(loss) and abs(float(loss) - torch.log(torch.tensor(float(cfg.vocab_size)))) < 1.0
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in m.parameters())
     assert m(x[:, :-1]).shape == (2, 16, cfg.vocab_size)
+
+
+def test_numa_placement_helpers(tmp_path, monkeypatch):
+    """utils/affinity.py: cpulist parsing, the sysfs lookups against a fake tree, and the no-op cases."""
+    import os
+
+    from akka_allreduce_b200.utils import affinity as A
+
+    assert A.parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert A.parse_cpulist("") == set()
+    dev = tmp_path / "bus/pci/devices/0000:19:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices/system/node/node1"
+    node.mkdir(parents=True)
+    allowed = sorted(os.sched_getaffinity(0))
+    (node / "cpulist").write_text(",".join(str(c) for c in allowed[: max(1, len(allowed) // 2)]))
+    assert A.numa_node_of_pci("0000:19:00.0", str(tmp_path)) == 1
+    assert A.numa_node_of_pci("0000:1A:00.0", str(tmp_path)) is None          # unknown device
+    (dev / "numa_node").write_text("-1\n")
+    assert A.numa_node_of_pci("0000:19:00.0", str(tmp_path)) is None          # platform does not say
+    (dev / "numa_node").write_text("1\n")
+    assert A.cpus_of_node(1, str(tmp_path)) == set(allowed[: max(1, len(allowed) // 2)])
+    assert A.cpus_of_node(7, str(tmp_path)) == set()
+    # bind_to_gpu end to end with a faked PCI address, restoring the mask afterwards
+    monkeypatch.setattr(A, "pci_address", lambda i: "0000:19:00.0")
+    before = os.sched_getaffinity(0)
+    try:
+        got = A.bind_to_gpu(0, str(tmp_path))
+        if len(allowed) >= 2:
+            assert got == {"numa_node": 1, "cpus": len(allowed) // 2}
+            assert os.sched_getaffinity(0) == set(allowed[: len(allowed) // 2])
+        else:
+            assert got is None
+    finally:
+        os.sched_setaffinity(0, before)
+    monkeypatch.setenv("AAR_NO_AFFINITY", "1")
+    assert A.bind_to_gpu(0, str(tmp_path)) is None
+    monkeypatch.delenv("AAR_NO_AFFINITY")
+    monkeypatch.setattr(A, "pci_address", lambda i: None)
+    assert A.bind_to_gpu(0, str(tmp_path)) is None
