@@ -14,6 +14,9 @@ from __future__ import annotations
 import os
 
 
+MIN_LOCAL_CPUS = 4
+
+
 def parse_cpulist(text: str) -> set[int]:
     """'0-3,8,10-11' -> {0,1,2,3,8,10,11} (the format of /sys/devices/system/node/nodeN/cpulist)."""
     cpus: set[int] = set()
@@ -67,8 +70,8 @@ def bind_to_gpu(device_index: int, sysfs: str = "/sys") -> dict | None:
     try:
         allowed = os.sched_getaffinity(0)
         local = cpus_of_node(node, sysfs) & allowed
-        if not local or local == allowed:
-            return None
+        if len(local) < MIN_LOCAL_CPUS or local == allowed:
+            return None  # nothing to gain, or too few local cores for the worker, IO and sampler threads
         os.sched_setaffinity(0, local)
     except OSError:
         return None
