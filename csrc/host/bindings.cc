@@ -215,6 +215,7 @@ PYBIND11_MODULE(_aar_host, m) {
       .def(py::init<>())
       .def_readwrite("rethrow", &WorkerOptions::rethrow)
       .def_readwrite("strict_partition", &WorkerOptions::strict_partition)
+      .def_readwrite("max_round_jump", &WorkerOptions::max_round_jump)
       .def_readwrite("verbose", &WorkerOptions::verbose);
 
   py::class_<WorkerEngine>(m, "WorkerEngine")

@@ -599,8 +599,12 @@ void WorkerNode::deliver(const Message& m) {
 
 void WorkerNode::on_local(const Message& m) { deliver(m); }
 
-void WorkerNode::on_frame(int /*conn_id*/, Frame kind, const uint8_t* p, size_t n) {
+void WorkerNode::on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) {
   Reader r{p, n};
+  // Control frames are the coordinator's: a connection that is not the one this worker opened to it cannot
+  // re-initialise the worker, start rounds or shut it down.
+  if ((kind == Frame::Init || kind == Frame::Start || kind == Frame::Shutdown) && conn_id != master_conn_)
+    throw std::runtime_error("control frame from a connection that is not the coordinator's");
   switch (kind) {
     case Frame::Init: {
       InitWorkers x;

@@ -99,7 +99,15 @@ void WorkerEngine::on_init(const InitWorkers& m) {
   for (auto& held : parked) handle(held);
 }
 
+void WorkerEngine::check_round(int round) const {
+  if (static_cast<int64_t>(round) - max_round_ > opts_.max_round_jump)
+    throw std::out_of_range("round " + std::to_string(round) + " is more than " +
+                            std::to_string(opts_.max_round_jump) + " rounds beyond round " +
+                            std::to_string(max_round_) + ", the newest started here: dropped");
+}
+
 void WorkerEngine::on_start(const StartAllreduce& m) {
+  check_round(m.round);
   max_round_ = std::max(max_round_, m.round);
   // Fallen more than maxLag behind: force every chunk of the oldest round out with
   // whatever has arrived, then complete it (AllreduceWorker.scala:100-106).  `round_`
@@ -126,6 +134,7 @@ void WorkerEngine::on_scatter(const ScatterBlock& m) {
     throw std::logic_error("scatter block for worker " + std::to_string(m.dest_id) +
                            " delivered to worker " + std::to_string(id_));
   if (m.round < round_ || completed_.count(m.round)) return;  // outdated
+  check_round(m.round);
   if (m.round <= max_round_) {
     const int row = m.round - round_;
     scatter_->store(m.value.data(), m.value.size(), row, m.src_id, m.chunk_id);
@@ -147,6 +156,7 @@ void WorkerEngine::on_reduce(const ReduceBlock& m) {
     throw std::runtime_error("Message with destination " + std::to_string(m.dest_id) +
                              " was incorrectly routed to node " + std::to_string(id_));
   if (m.round < round_ || completed_.count(m.round)) return;  // outdated
+  check_round(m.round);
   if (m.round <= max_round_) {
     const int row = m.round - round_;
     reduce_->store(m.value.data(), m.value.size(), row, m.src_id, m.chunk_id, m.count);

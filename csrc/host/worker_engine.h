@@ -37,6 +37,11 @@ struct WorkerOptions {
   // (n=9, P=4).  When false (default) trailing owners get empty blocks.
   bool strict_partition = false;
   bool verbose = false;
+  // A message may name a round this far beyond the newest one started here, no further.  The catch-up path
+  // force-completes every round in between (AllreduceWorker.scala:100-106), so a corrupt or hostile round number
+  // would otherwise keep the handler busy for billions of iterations; a worker that is legitimately this far
+  // behind has long been declared dead by the coordinator.  Messages beyond the bound are recorded as errors.
+  int max_round_jump = 1 << 16;
 };
 
 class WorkerEngine {
@@ -60,6 +65,7 @@ class WorkerEngine {
 
  private:
   void on_init(const InitWorkers& m);
+  void check_round(int round) const;  // throws for a round absurdly far ahead (WorkerOptions::max_round_jump)
   void on_start(const StartAllreduce& m);
   void on_scatter(const ScatterBlock& m);
   void on_reduce(const ReduceBlock& m);

@@ -308,3 +308,50 @@ def test_cli_reads_the_config_file_without_being_told(tmp_path, monkeypatch):
     assert build_config(["2600", "3"]).worker.totalSize == 3          # the command line still wins
     monkeypatch.delenv("AAR_CONFIG")
     assert build_config([]).worker.totalSize == 2                     # conf/application.conf
+
+
+@pytest.mark.timeout(120)
+def test_workers_survive_garbage_on_their_ports():
+    """Random frames of every kind (valid lengths, random payloads) at the workers' own listening ports while a job
+    runs: control frames are only taken from the coordinator's connection, absurd round numbers are dropped, and
+    the job keeps making progress and shuts down cleanly.  (Before those two checks a random StartAllreduce frame
+    sent the worker into a catch-up loop of billions of rounds.)"""
+    import random
+    import socket
+    import struct
+
+    rng = random.Random(5)
+    cfg = _cluster(2, 64, 8, 10 ** 8)
+    master = AllreduceMaster(cfg)
+    mport = master.start()
+    workers = []
+    for _ in range(2):
+        w = AllreduceWorker(lambda req: AllReduceInput(np.ones(64, dtype=np.float32)), lambda out: None,
+                            master_port=mport)
+        w.start()
+        workers.append(w)
+    try:
+        t0 = time.time()
+        while master.round < 10 and time.time() - t0 < 20:
+            time.sleep(0.01)
+        ports = [w._node.port for w in workers]
+        for _ in range(150):
+            try:
+                s = socket.create_connection(("127.0.0.1", rng.choice(ports)), timeout=2)
+                for _ in range(rng.randint(1, 20)):
+                    n = rng.choice([0, 1, 3, 4, 7, 16, 40, 200, 5000])
+                    s.sendall(struct.pack("<IB", n, rng.randint(0, 12)) + os.urandom(n))
+                s.close()
+            except OSError:
+                pass
+        r0 = master.round
+        t0 = time.time()
+        while master.round < r0 + 50 and time.time() - t0 < 20:
+            time.sleep(0.01)
+        assert master.round >= r0 + 50 and master.alive == 2, (master.round, r0, master.alive)
+    finally:
+        t0 = time.time()
+        for w in workers:
+            w.stop()
+        master.stop()
+    assert time.time() - t0 < 10          # stop() does not hang on a wedged IO thread

@@ -433,3 +433,23 @@ def test_messages_before_init_are_replayed():
     t.expect_no_msg()
     t.init(t.peers_as_probe(4), 4, 0, 1, 1, 5, 8, 2)
     _expect_basic_scatter(t, 0)
+
+
+def test_absurd_round_numbers_are_dropped_not_replayed():
+    """Not in the reference (its catch-up loop would run for as many rounds as the message names): a Start, Scatter
+    or Reduce naming a round more than `max_round_jump` ahead is recorded as an error and dropped; the worker
+    keeps working.  A large but plausible jump still catches up."""
+    hs = Harness(size=8)
+    hs.init(hs.peers_as_probe(2, real=0), 2, 0, 1.0, 1.0, 1, 8, 2)
+    hs.tell(h.StartAllreduce(0))
+    while hs.fifo:
+        hs.next()
+    before = len(hs.worker.errors)
+    hs.tell(h.StartAllreduce(2 ** 30))
+    hs.tell(h.ScatterBlock(np.ones(2, dtype=np.float32), 1, 0, 0, 2 ** 30))
+    hs.tell(h.ReduceBlock(np.ones(2, dtype=np.float32), 1, 0, 0, 2 ** 30, 2))
+    assert len(hs.worker.errors) == before + 3 and all("rounds beyond" in e for e in hs.worker.errors[before:])
+    assert hs.worker.max_round == 0 and hs.bus.pending() == 0
+    hs.expect_no_msg()
+    hs.tell(h.StartAllreduce(500))           # far, but legitimate: force-completes 0..498 and scatters up to 500
+    assert hs.worker.max_round == 500 and hs.worker.round == 499
