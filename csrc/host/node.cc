@@ -472,6 +472,12 @@ void MasterNode::on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) {
       CompleteAllreduce c;
       c.src_id = r.get<int32_t>();
       c.round = r.get<int32_t>();
+      // a completion report counts towards the thAllreduce gate: only the registered worker holding that id may
+      // send it (a stray connection must not be able to open rounds)
+      const auto owner = engine_.workers().find(c.src_id);
+      if (owner == engine_.workers().end() || owner->second != kConnBase + conn_id)
+        throw std::runtime_error("completion report for worker " + std::to_string(c.src_id) +
+                                 " from a connection that does not hold that id");
       engine_.handle(c);
       note_progress();
       break;
