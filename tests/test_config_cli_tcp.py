@@ -355,3 +355,49 @@ def test_workers_survive_garbage_on_their_ports():
             w.stop()
         master.stop()
     assert time.time() - t0 < 10          # stop() does not hang on a wedged IO thread
+
+
+def test_handler_mode_worker_node_drives_the_coordinator():
+    """The plumbing `DeviceWorker` uses, without a GPU: a WorkerNode with a Python message handler instead of an
+    engine.  InitWorkers hands out the id, every StartAllreduce is answered with report_complete(id, round), and the
+    coordinator (which only counts a report from the connection holding that id) runs through all rounds."""
+    import threading
+
+    from akka_allreduce_b200 import host
+
+    cfg = _cluster(3, 16, 4, 40)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    nodes, state = [], []
+    for i in range(3):
+        opts = host.WorkerNodeOptions()
+        node = host.WorkerNode("127.0.0.1", port, None, None, opts)
+        st = {"id": -1, "started": -1, "reported": -1, "lock": threading.Lock()}
+
+        def on_message(msg, node=node, st=st):
+            with st["lock"]:
+                if isinstance(msg, host.InitWorkers) and st["id"] < 0:
+                    st["id"] = msg.dest_id
+                    assert msg.worker_num == 3 and msg.data_size == 16 and msg.max_chunk_size == 4
+                elif isinstance(msg, host.StartAllreduce):
+                    st["started"] = max(st["started"], msg.round)
+                if st["id"] >= 0:
+                    while st["reported"] < st["started"]:
+                        st["reported"] += 1
+                        node.report_complete(st["id"], st["reported"])
+
+        node.set_handler(on_message)
+        node.listen("127.0.0.1", 0)
+        node.begin()
+        nodes.append(node)
+        state.append(st)
+    try:
+        assert master.wait(30.0), f"master stuck at round {master.round}"
+        assert sorted(s["id"] for s in state) == [0, 1, 2]
+        assert all(s["reported"] == 40 for s in state)
+        # a report for somebody else's id is not counted (and does not disturb anything)
+        nodes[0].report_complete(state[1]["id"], 41)
+    finally:
+        for n in nodes:
+            n.stop()
+        master.stop()
