@@ -34,6 +34,8 @@ HOST_SOURCES = [
     "host/master_engine.cc",
     "host/local_bus.cc",
     "host/node.cc",
+    "host/shm_cluster.cc",
+    "host/shm_bindings.cc",
     "host/node_bindings.cc",
     "host/bindings.cc",
 ]
@@ -175,6 +177,24 @@ def build_cpu_cluster(force: bool = False) -> Path:
         tmp = out.with_suffix(".tmp%d" % os.getpid())
         _run(["g++", "-std=c++17", "-O2", "-Wall", "-Wno-unused-parameter", f"-I{INCLUDE}", f"-I{CSRC / 'host'}",
               "-o", str(tmp)] + [str(s) for s in srcs] + ["-lpthread"])
+        os.replace(tmp, out)
+        _record(out, deps)
+    return out
+
+
+def build_shm_cluster(force: bool = False) -> Path:
+    """Stand-alone binary of the shared-memory restatement of the device protocol (csrc/host/shm_cluster.h):
+    ``build/aar_shm_cluster [world n maxChunkSize maxLag rounds thReduce thComplete thAllreduce stallProb stallUs timeoutMs]``."""
+    out = ROOT / "build" / "aar_shm_cluster"
+    srcs = [CSRC / "host/shm_cluster.cc", CSRC / "host/shm_cluster_main.cc"]
+    deps = srcs + _headers()
+    if not force and not _stale(out, deps):
+        return out
+    with _BuildLock():
+        (ROOT / "build").mkdir(exist_ok=True)
+        tmp = out.with_suffix(".tmp%d" % os.getpid())
+        _run(["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", f"-I{INCLUDE}", f"-I{CSRC / 'host'}", "-o", str(tmp)] +
+             [str(s) for s in srcs] + ["-lpthread"])
         os.replace(tmp, out)
         _record(out, deps)
     return out

@@ -43,3 +43,6 @@ MasterNode = _lib.MasterNode
 WorkerNodeOptions = _lib.WorkerNodeOptions
 WorkerNode = _lib.WorkerNode
 ThroughputStats = _lib.ThroughputStats
+# device protocol restated for CPU threads in shared memory (csrc/host/shm_cluster.h)
+ShmConfig = _lib.ShmConfig
+ShmCluster = _lib.ShmCluster

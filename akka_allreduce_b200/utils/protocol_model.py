@@ -53,6 +53,9 @@ class ModelConfig:
                                # launch, i.e. before the gate and without the destination mask
     output_view: bool = False  # zero-copy output (`output_view`): the caller keeps reading round r's sink slot until it
                                # launches round r+L (the worker loop delivers sink(r) before that launch)
+    notices: bool = False      # skip notices (implemented in csrc/host/shm_cluster.cc, a candidate for the kernel): a sender
+                               # that leaves a peer out records the tag in a per-(dest, src) word outside the slot ring,
+                               # and a waiter treats "not arrived + notice >= my tag" as "will never arrive"
     oneshot_backpressure: bool = False  # the one-shot kernel as it is has NO destination mask;
                                         # True models the planned fix (same `done + L >= tag` rule as two-shot)
 
@@ -75,7 +78,8 @@ class _Layout:
         self.o_scat = self.o_arr + P * L * P
         self.o_rfl = self.o_scat + P * L * P
         self.o_sink = self.o_rfl + P * L * P
-        self.size = self.o_sink + P * L * P
+        self.o_note = self.o_sink + P * L * P
+        self.size = self.o_note + P * P
 
     def done(self, q, s):
         return self.o_done + q * self.P + s
@@ -91,6 +95,9 @@ class _Layout:
 
     def sink(self, q, l, s):
         return self.o_sink + (q * self.L + l) * self.P + s
+
+    def note(self, q, s):
+        return self.o_note + q * self.P + s
 
 
 def _put(mem: tuple, writes) -> tuple:
@@ -110,7 +117,7 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
     req_c = cfg.req_complete or P
     lay = _Layout(P, L)
     full = (1 << P) - 1
-    exact = req_r == P and req_c == P and not cfg.timeouts
+    exact = req_r == P and req_c == P and not cfg.timeouts and not cfg.notices
 
     # rank state: (tag, pc, i, ok_mask, mask)
     init = (tuple((1, GATE, 0, 0, 0) for _ in range(P)), tuple([0] * lay.size), cfg.giveups if cfg.timeouts else 0)
@@ -163,7 +170,8 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                     for d in range(P):
                         if d == q or mem[lay.done(q, d)] + L >= t:
                             okm |= 1 << d
-                yield go((t, SDATA, 0, okm, 0))
+                notes = [(lay.note(d, q), t) for d in range(P) if not (okm >> d) & 1] if cfg.notices else []
+                yield go((t, SDATA, 0, okm, 0), notes)
             elif pc == SDATA:
                 # two-shot: my slice for owner d into d's scat row [me]; one-shot: my whole message, same rows
                 writes = [] if cfg.early_write else [(lay.scat(d, l, q), t) for d in range(P) if (ok >> d) & 1]
@@ -179,6 +187,9 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                     if mem[lay.arr(q, l, s)] == t:
                         have |= 1 << s
                 met = bin(have).count("1") >= req_r
+                if not met and cfg.notices:   # everyone who has not arrived has said it never will
+                    gone = [s for s in range(P) if not (have >> s) & 1 and mem[lay.note(q, s)] >= t]
+                    met = bool(gone) and bin(have).count("1") + len(gone) == P
                 if met or may_give_up:
                     yield go((t, RREAD, 0, ok, have), gave_up=not met)
             elif pc == RREAD:
@@ -209,6 +220,9 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                     if mem[lay.rfl(q, l, o)] == t:
                         have |= 1 << o
                 met = bin(have).count("1") >= req_c
+                if not met and cfg.notices:
+                    gone = [o for o in range(P) if not (have >> o) & 1 and mem[lay.note(q, o)] >= t]
+                    met = bool(gone) and bin(have).count("1") + len(gone) == P
                 if met or may_give_up:
                     yield go((t, CREAD, 0, ok, have), gave_up=not met)
             elif pc == CREAD:
@@ -299,11 +313,12 @@ if __name__ == "__main__":
     ap.add_argument("--oneshot-backpressure", action="store_true")
     ap.add_argument("--early-write", action="store_true")
     ap.add_argument("--output-view", action="store_true")
+    ap.add_argument("--notices", action="store_true")
     ap.add_argument("--walks", type=int, default=0, help="random executions instead of the exhaustive search")
     ap.add_argument("--seed", type=int, default=0)
     a = ap.parse_args()
     cfg = ModelConfig(a.P, a.L, a.rounds, a.req_reduce, a.req_complete, a.gate, a.timeouts, a.giveups, a.oneshot,
-                      not a.no_backpressure, a.early_write, a.output_view, a.oneshot_backpressure)
+                      not a.no_backpressure, a.early_write, a.output_view, a.notices, a.oneshot_backpressure)
     t0 = time.time()
     r = check(cfg, walks=a.walks, seed=a.seed)
     print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")

@@ -14,6 +14,10 @@
 #include "node.h"
 #include "worker_engine.h"
 
+namespace aar {
+void bind_shm(pybind11::module_& m);
+}
+
 namespace py = pybind11;
 using namespace aar;
 
@@ -293,4 +297,5 @@ PYBIND11_MODULE(_aar_host, m) {
            "Remove and return everything the probe has received so far");
 
   bind_nodes(m);
+  bind_shm(m);
 }
