@@ -101,3 +101,17 @@ def test_random_executions_at_eight_ranks():
     r = check(ModelConfig(P=6, L=2, rounds=10, req_reduce=4, req_complete=4, gate_count=4, timeouts=True,
                           backpressure=False), walks=300, seed=3)
     assert not r.ok and "carries tag" in r.violation
+
+
+def test_skip_notices_make_partial_thresholds_live_without_timeouts():
+    """Without notices a rank that its peers left out (back-pressure) waits for data that was never sent: with
+    thresholds below 1 and no timeouts the search finds stuck states.  With notices ("highest tag for which I left
+    you out", one word per pair, outside the slot ring) every configuration below is live and still safe — even one
+    slot without the gate.  Implemented in csrc/host/shm_cluster.cc; a candidate for the kernel."""
+    stuck = check(ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2))
+    assert not stuck.ok and stuck.violation.startswith("stuck")
+    assert check(ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2, notices=True)).ok
+    assert check(ModelConfig(P=2, L=1, rounds=4, notices=True)).ok
+    assert check(ModelConfig(P=2, L=2, rounds=5, req_reduce=1, req_complete=1, notices=True, timeouts=True)).ok
+    assert check(ModelConfig(P=8, L=2, rounds=8, req_reduce=6, req_complete=6, gate_count=6, notices=True),
+                 walks=40, seed=4).ok
