@@ -32,6 +32,8 @@ void bind_shm(py::module_& m) {
       .def_readwrite("th_complete", &ShmConfig::th_complete)
       .def_readwrite("th_allreduce", &ShmConfig::th_allreduce)
       .def_readwrite("timeout_ms", &ShmConfig::timeout_ms)
+      .def_readwrite("scale", &ShmConfig::scale)
+      .def_readwrite("normalize", &ShmConfig::normalize)
       .def_readwrite("skip_notice", &ShmConfig::skip_notice);
 
   py::class_<ShmCluster>(m, "ShmCluster")

@@ -157,7 +157,12 @@ ShmRoundInfo ShmCluster::rank_round(int rank, int round, const float* src, float
       uint32_t* arr = reinterpret_cast<uint32_t*>(region(d) + sym_.off_arr);
       for (int ch = 0; ch < nch; ++ch) {
         const int64_t cb = chunk_begin(ch, cfg_.max_chunk, bsize), ce = chunk_end(ch, cfg_.max_chunk, bsize);
-        std::memcpy(row + cb, src + part_.start(d) + cb, static_cast<size_t>(ce - cb) * sizeof(float));
+        if (cfg_.scale == 1.f) {
+          std::memcpy(row + cb, src + part_.start(d) + cb, static_cast<size_t>(ce - cb) * sizeof(float));
+        } else {
+          const float* from = src + part_.start(d);
+          for (int64_t k = cb; k < ce; ++k) row[k] = from[k] * cfg_.scale;
+        }
         st_release(arr + sym_.arr_index(slot, rank, ch), tag);
       }
     }
@@ -198,6 +203,10 @@ ShmRoundInfo ShmCluster::rank_round(int rank, int round, const float* src, float
           if (!((have >> s) & 1u)) continue;
           const float* r = rows + sym_.scat_elem(slot, s) + cb;
           for (int64_t k = 0; k < len; ++k) acc[static_cast<size_t>(k)] += r[k];
+        }
+        if (cfg_.normalize && cnt > 0) {
+          const float post = 1.f / static_cast<float>(cnt);
+          for (int64_t k = 0; k < len; ++k) acc[static_cast<size_t>(k)] *= post;
         }
         for (int i = 0; i < P; ++i) {
           const int d = (i + rank) % P;

@@ -34,6 +34,8 @@ struct ShmConfig {
   float th_reduce = 1.f, th_complete = 1.f;
   float th_allreduce = 1.f;  // <= 0: no gate
   double timeout_ms = 2000.0;
+  float scale = 1.f;       // source scale fused into the scatter (the kernel's `scale`)
+  bool normalize = false;  // divide every reduced chunk by its contributor count (the kernel's `normalize`)
   // Extension over the kernel's protocol (candidate for it): a sender that leaves a peer out because of
   // back-pressure says so in a word of its own, so the peer does not sit out a timeout waiting for data that was
   // never sent.  See "skip notices" in shm_cluster.cc.

@@ -133,3 +133,21 @@ def test_native_shm_cluster_binary():
     for argv in (["4", "778", "3", "3", "500"], ["8", "4096", "64", "2", "300", "0.75", "0.75", "0.75", "0.01", "100", "500"]):
         p = subprocess.run([exe] + argv, capture_output=True, text=True, timeout=120, env=env)
         assert p.returncode == 0 and "0 mismatches" in p.stdout and "0 timeouts" in p.stdout, p.stdout + p.stderr
+
+
+def test_scale_and_normalize_like_the_kernel():
+    """`scale` multiplies every contribution on its way out, `normalize` divides a reduced chunk by its contributor
+    count: with a silent rank the mean is over the three that spoke (what the DDP hook relies on)."""
+    c = host.ShmConfig()
+    c.world, c.n, c.max_chunk, c.max_lag = 4, 48, 6, 1
+    c.th_allreduce, c.th_reduce, c.th_complete = 1.0, 0.75, 1.0
+    c.scale, c.normalize, c.timeout_ms = 0.5, True, 5000.0
+    cl = host.ShmCluster(c)
+    srcs = [np.full(48, float(r + 1), dtype=np.float32) for r in range(4)]
+    outs, counts, _ = cl.run_round(0, srcs, mute_mask=1 << 3)
+    assert (counts[0] == 3).all() and np.allclose(outs[0], 0.5 * (1 + 2 + 3) / 3)
+    outs, counts, _ = cl.run_round(1, srcs)
+    full = counts[0] == 4            # a chunk fires as soon as 3 are in: 3 or 4 contributors, mean either way
+    assert np.isin(counts[0], (3, 4)).all() and np.allclose(outs[0][full], 0.5 * 10 / 4)
+    three = {round(0.5 * (10 - v) / 3, 5) for v in (1, 2, 3, 4)}        # whichever rank was not waited for
+    assert all(round(float(x), 5) in three for x in outs[0][~full])
