@@ -55,7 +55,7 @@ class ClusterConfig:
 
 @dataclass
 class DeviceConfig:
-    backend: str = "cpu"       # cpu | cuda
+    backend: str = "cpu"       # cpu (TCP) | shm (device protocol in shared memory, one host) | cuda
     algo: str = "auto"         # auto | oneshot | twoshot | nvls
     dtype: str = "float32"     # wire dtype of the symmetric slots: float32 | bfloat16
     normalize: bool = False    # divide by the contributor count in the kernel epilogue

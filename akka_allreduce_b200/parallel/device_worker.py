@@ -174,7 +174,8 @@ class DeviceWorker:
             self.round = r + 1
             self.rounds_completed += 1
 
-        last = cfg.data.maxRound
+        # the coordinator says where the job ends (InitWorkers.max_round); without that, the local configuration
+        last = init.max_round if init.max_round >= 0 else cfg.data.maxRound
         r = init.start_round  # 0 unless the master initialised us into a running job
         while r <= last:
             with self._cv:

@@ -90,15 +90,20 @@ class AllreduceWorker:
 
 def create_worker(data_source: DataSource, data_sink: DataSink, config: AllreduceConfig,
                   master_host: str | None = None, master_port: int | None = None, **kwargs):
-    """One constructor for both backends: ``config.device.backend`` picks the CPU worker (C++ protocol engine
-    over TCP) or the CUDA worker (fused kernel over NVLink); the callbacks and the contract are the same."""
+    """One constructor for every backend: ``config.device.backend`` picks the CPU worker (C++ protocol engine over
+    TCP), the shared-memory worker (the device protocol over POSIX shared memory, one host) or the CUDA worker (fused
+    kernel over NVLink); the callbacks and the contract are the same."""
     host_, port_ = master_host or config.cluster.host, master_port or config.cluster.port
     if config.device.backend == "cuda":
         from .parallel.device_worker import DeviceWorker
 
         return DeviceWorker(data_source, data_sink, config, host_, port_, **kwargs)
+    if config.device.backend == "shm":
+        from .parallel.shm_worker import ShmWorker
+
+        return ShmWorker(data_source, data_sink, config, host_, port_, **kwargs)
     if config.device.backend != "cpu":
-        raise ValueError(f"unknown backend {config.device.backend!r} (cpu | cuda)")
+        raise ValueError(f"unknown backend {config.device.backend!r} (cpu | shm | cuda)")
     return AllreduceWorker(data_source, data_sink, host_, port_, heartbeat=config.cluster.heartbeat,
                            loglevel=config.cluster.loglevel, **kwargs)
 
@@ -117,6 +122,11 @@ def start_up(port: int | str = 0, data_size: int = 10, checkpoint: int = 50, ass
 
         return start_device_worker(config or AllreduceConfig(), data_size, checkpoint, assert_multiple,
                                    master_host, master_port)
+    if backend == "shm":
+        from .parallel.shm_worker import start_shm_worker
+
+        return start_shm_worker(config or AllreduceConfig(), data_size, checkpoint, assert_multiple, master_host,
+                                master_port)
     w = AllreduceWorker.builtin(data_size, checkpoint, assert_multiple, master_host, master_port, int(port))
     w.start()
     return w
@@ -132,7 +142,7 @@ def main(argv: list[str] | None = None) -> int:
     ap.add_argument("--master-port", type=int)
     ap.add_argument("--checkpoint", type=int)
     ap.add_argument("--assert-multiple", type=int)
-    ap.add_argument("--backend", choices=["cpu", "cuda"])
+    ap.add_argument("--backend", choices=["cpu", "shm", "cuda"])
     a = ap.parse_args(sys.argv[1:] if argv is None else argv)
     # like the reference, whose application.conf is picked up without being named: the checkout's (or the
     # packaged) application.conf is read unless --config / AAR_CONFIG names another file

@@ -108,6 +108,7 @@ PYBIND11_MODULE(_aar_host, m) {
       .def_readwrite("data_size", &InitWorkers::data_size)
       .def_readwrite("max_chunk_size", &InitWorkers::max_chunk_size)
       .def_readwrite("start_round", &InitWorkers::start_round)
+      .def_readwrite("max_round", &InitWorkers::max_round)
       .def("__repr__", [](const InitWorkers& x) { return describe(Message(x)); });
 
   py::class_<StartAllreduce>(m, "StartAllreduce")

@@ -83,6 +83,7 @@ void MasterEngine::init_workers(int start_round) {
     init.data_size = cfg_.data_size;
     init.max_chunk_size = cfg_.max_chunk_size;
     init.start_round = start_round;
+    init.max_round = cfg_.max_round;
     mailer_->send(ep, std::move(init));
   }
 }

@@ -29,6 +29,10 @@ struct InitWorkers {
   // Extension (not in the reference): first round a worker that joins a RUNNING job takes part in.
   // 0 for the initial broadcast, so the normal start-up is message-for-message the reference's.
   int start_round = 0;
+  // Extension: the last round of the job (maxRound), -1 = not told.  The reference's workers never learn it — they
+  // only react to StartAllreduce — but a worker that gates rounds itself (device / shared-memory gate) has to know
+  // where to stop.
+  int max_round = -1;
 };
 
 struct StartAllreduce {

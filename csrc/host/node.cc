@@ -415,6 +415,7 @@ void MasterNode::send(Endpoint to, Message msg) {
       w.put<int64_t>(x.data_size);
       w.put<int64_t>(x.max_chunk_size);
       w.put<int32_t>(x.start_round);
+      w.put<int32_t>(x.max_round);
       w.put<uint32_t>(static_cast<uint32_t>(x.workers.size()));
       for (const auto& [id, ep] : x.workers) {
         const PeerAddress& a = addr_of_conn_[static_cast<int>(ep - kConnBase)];
@@ -622,6 +623,7 @@ void WorkerNode::on_frame(int conn_id, Frame kind, const uint8_t* p, size_t n) {
       x.data_size = r.get<int64_t>();
       x.max_chunk_size = r.get<int64_t>();
       x.start_round = r.get<int32_t>();
+      x.max_round = r.get<int32_t>();
       x.master = kMasterEp;
       const uint32_t peers = r.get<uint32_t>();
       const PeerAddress me{listen_host_, listen_port_};

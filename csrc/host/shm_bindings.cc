@@ -38,12 +38,41 @@ void bind_shm(py::module_& m) {
 
   py::class_<ShmCluster>(m, "ShmCluster")
       .def(py::init<const ShmConfig&>())
+      .def_static(
+          "attach",
+          [](const ShmConfig& cfg, const std::string& name, bool create, double timeout_s, bool accept_orphan) {
+            py::gil_scoped_release nogil;
+            return std::make_unique<ShmCluster>(cfg, name, create, timeout_s, accept_orphan);
+          },
+          py::arg("config"), py::arg("name"), py::arg("create"), py::arg("timeout_s") = 30.0,
+          py::arg("accept_orphan") = false,
+          "Cluster whose regions live in the named POSIX shared-memory segment (one process per rank)")
+      .def(
+          "rank_round",
+          [](ShmCluster& c, int rank, int round, FloatArray src) {
+            const int64_t n = c.layout().n;
+            if (src.size() != n) throw std::invalid_argument("Input data size is different from initialization time!");
+            py::array_t<float> out(n);
+            py::array_t<int32_t> counts(n);
+            ShmRoundInfo info;
+            {
+              const float* in = src.data();
+              float* o = out.mutable_data();
+              int32_t* k = counts.mutable_data();
+              py::gil_scoped_release nogil;
+              info = c.rank_round(rank, round, in, o, k, nullptr);
+            }
+            return py::make_tuple(out, counts, info_dict(info));
+          },
+          py::arg("rank"), py::arg("round"), py::arg("src"),
+          "One rank's round (blocks until that rank has completed it): returns (out, counts, info)")
       .def_property_readonly("req_reduce", &ShmCluster::req_reduce)
       .def_property_readonly("req_complete", &ShmCluster::req_complete)
       .def_property_readonly("gate_count", &ShmCluster::gate_count)
       .def_property_readonly("total_chunks", &ShmCluster::total_chunks)
       .def_property_readonly("region_bytes", [](const ShmCluster& c) { return c.layout().total_bytes; })
       .def_property_readonly("next_round", &ShmCluster::next_round)
+      .def("issued", &ShmCluster::issued)
       .def("force_complete", &ShmCluster::force_complete)
       .def(
           "run_round",

@@ -10,6 +10,13 @@
 #include <string>
 #include <thread>
 
+#include <fcntl.h>
+#include <signal.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include <cerrno>
+
 namespace aar {
 
 namespace {
@@ -40,9 +47,26 @@ inline void relax(int& spins) {
 
 }  // namespace
 
-void ShmCluster::AlignedFree::operator()(uint8_t* p) const { std::free(p); }
+namespace {
+struct ShmHeader {  // first words of a shared segment
+  uint32_t magic, ready;
+  int32_t world, max_lag;
+  int64_t n, max_chunk;
+  uint64_t total_bytes;
+  int64_t owner_pid;
+};
+constexpr uint32_t kShmMagic = 0x41415253u;  // "AARS"
+constexpr size_t kHeaderBytes = 256;
+}  // namespace
 
-ShmCluster::ShmCluster(const ShmConfig& cfg) : cfg_(cfg) {
+size_t ShmCluster::control_bytes() {
+  // header + force[16] + progress[16] + next_round[16] + notice[16*16], rounded to a page
+  return static_cast<size_t>(SymLayout::up(kHeaderBytes + 3 * kMaxRanks * 4 + kMaxRanks * kMaxRanks * 4, 4096));
+}
+size_t ShmCluster::region_bytes() const { return static_cast<size_t>(SymLayout::up(sym_.total_bytes, 4096)); }
+
+void ShmCluster::init_geometry() {
+  const ShmConfig& cfg = cfg_;
   if (cfg.world < 1 || cfg.world > kMaxRanks) throw std::invalid_argument("ShmCluster: world must be 1..16");
   if (cfg.n <= 0 || cfg.max_chunk <= 0 || cfg.max_lag < 0) throw std::invalid_argument("ShmCluster: bad size arguments");
   L_ = cfg.max_lag + 1;
@@ -54,23 +78,117 @@ ShmCluster::ShmCluster(const ShmConfig& cfg) : cfg_(cfg) {
   gate_count_ = 0;
   if (cfg.th_allreduce > 0.f)  // smallest k with master_gate(k) true (AllreduceMaster.scala:58)
     while (gate_count_ < cfg.world && !master_gate(gate_count_, cfg.world, cfg.th_allreduce)) ++gate_count_;
-  for (int r = 0; r < cfg.world; ++r) {
-    const size_t bytes = static_cast<size_t>(SymLayout::up(sym_.total_bytes, 4096));
-    uint8_t* p = static_cast<uint8_t*>(std::aligned_alloc(4096, bytes));
-    if (p == nullptr) throw std::bad_alloc();
-    std::memset(p, 0, bytes);
-    regions_.emplace_back(p);
+  block_bytes_ = control_bytes() + static_cast<size_t>(cfg.world) * region_bytes();
+}
+
+void ShmCluster::place(uint8_t* block) {
+  // Zero-filled memory is a valid initial state for every word below (lock-free 32-bit atomics, value 0).
+  block_ = block;
+  uint8_t* p = block + kHeaderBytes;
+  force_ = reinterpret_cast<std::atomic<uint32_t>*>(p);
+  p += kMaxRanks * 4;
+  progress_ = reinterpret_cast<std::atomic<int>*>(p);
+  p += kMaxRanks * 4;
+  next_round_ = reinterpret_cast<std::atomic<int>*>(p);
+  p += kMaxRanks * 4;
+  notice_ = reinterpret_cast<std::atomic<uint32_t>*>(p);
+  regions_.clear();
+  for (int r = 0; r < cfg_.world; ++r) regions_.push_back(block + control_bytes() + static_cast<size_t>(r) * region_bytes());
+}
+
+ShmCluster::ShmCluster(const ShmConfig& cfg) : cfg_(cfg) {
+  static_assert(sizeof(std::atomic<uint32_t>) == 4 && sizeof(std::atomic<int>) == 4, "control words are 32-bit");
+  init_geometry();
+  uint8_t* p = static_cast<uint8_t*>(std::aligned_alloc(4096, block_bytes_));
+  if (p == nullptr) throw std::bad_alloc();
+  std::memset(p, 0, block_bytes_);
+  place(p);
+}
+
+ShmCluster::ShmCluster(const ShmConfig& cfg, const std::string& shm_name, bool create, double attach_timeout_s,
+                       bool accept_orphan)
+    : cfg_(cfg), shm_name_(shm_name), shm_owner_(create) {
+  init_geometry();
+  if (shm_name.empty() || shm_name[0] != '/') throw std::invalid_argument("ShmCluster: shared memory name must start with '/'");
+  int fd = -1;
+  if (create) {
+    shm_unlink(shm_name.c_str());  // a stale segment of a crashed run
+    fd = shm_open(shm_name.c_str(), O_CREAT | O_EXCL | O_RDWR, 0600);
+    if (fd < 0) throw std::runtime_error("shm_open(" + shm_name + ", create): " + std::strerror(errno));
+    if (ftruncate(fd, static_cast<off_t>(block_bytes_)) != 0) {
+      const std::string why = std::strerror(errno);
+      close(fd);
+      shm_unlink(shm_name.c_str());
+      throw std::runtime_error("ftruncate(" + shm_name + "): " + why);
+    }
+  } else {
+    const auto give_up = Clock::now() + std::chrono::duration_cast<Clock::duration>(std::chrono::duration<double>(attach_timeout_s));
+    for (;;) {  // the creator may not have got there yet, or the name may still point at a dead run's segment
+      fd = shm_open(shm_name.c_str(), O_RDWR, 0600);
+      struct stat st {};
+      if (fd >= 0 && fstat(fd, &st) == 0 && static_cast<size_t>(st.st_size) >= kHeaderBytes) {
+        ShmHeader h{};
+        const bool got = pread(fd, &h, sizeof(h), 0) == static_cast<ssize_t>(sizeof(h));
+        const bool live = got && h.magic == kShmMagic && h.ready == 1u && h.owner_pid > 0 &&
+                          (kill(static_cast<pid_t>(h.owner_pid), 0) == 0 || errno == EPERM);
+        if (got && h.magic == kShmMagic && h.ready == 1u && (live || accept_orphan) &&
+            static_cast<size_t>(st.st_size) >= block_bytes_)
+          break;
+      }
+      if (fd >= 0) close(fd);
+      fd = -1;
+      if (Clock::now() > give_up) throw std::runtime_error("shared memory segment " + shm_name + " did not appear");
+      std::this_thread::sleep_for(std::chrono::milliseconds(5));
+    }
   }
-  force_.reset(new std::atomic<uint32_t>[static_cast<size_t>(cfg.world)]);
-  progress_.reset(new std::atomic<int>[static_cast<size_t>(cfg.world)]);
-  next_round_.reset(new std::atomic<int>[static_cast<size_t>(cfg.world)]);
-  notice_.reset(new std::atomic<uint32_t>[static_cast<size_t>(cfg.world) * cfg.world]);
-  for (int i = 0; i < cfg.world * cfg.world; ++i) notice_[static_cast<size_t>(i)].store(0);
-  for (int r = 0; r < cfg.world; ++r) {
-    force_[static_cast<size_t>(r)].store(0);
-    progress_[static_cast<size_t>(r)].store(0);
-    next_round_[static_cast<size_t>(r)].store(0);
+  void* m = mmap(nullptr, block_bytes_, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+  close(fd);
+  if (m == MAP_FAILED) {
+    if (create) shm_unlink(shm_name.c_str());
+    throw std::runtime_error("mmap(" + shm_name + "): " + std::strerror(errno));
   }
+  place(static_cast<uint8_t*>(m));  // (a fresh segment is zero-filled by the kernel)
+  auto* hdr = reinterpret_cast<ShmHeader*>(block_);
+  uint32_t* ready = &hdr->ready;
+  if (create) {
+    hdr->magic = kShmMagic;
+    hdr->world = cfg.world;
+    hdr->max_lag = cfg.max_lag;
+    hdr->n = cfg.n;
+    hdr->max_chunk = cfg.max_chunk;
+    hdr->total_bytes = block_bytes_;
+    hdr->owner_pid = static_cast<int64_t>(getpid());
+    st_release(ready, 1u);
+  } else {
+    const auto give_up = Clock::now() + std::chrono::duration_cast<Clock::duration>(std::chrono::duration<double>(attach_timeout_s));
+    while (ld_acquire(ready) != 1u) {
+      if (Clock::now() > give_up) {
+        munmap(block_, block_bytes_);
+        throw std::runtime_error("shared memory segment " + shm_name + " was never initialised");
+      }
+      std::this_thread::sleep_for(std::chrono::milliseconds(1));
+    }
+    if (hdr->magic != kShmMagic || hdr->world != cfg.world || hdr->max_lag != cfg.max_lag || hdr->n != cfg.n ||
+        hdr->max_chunk != cfg.max_chunk || hdr->total_bytes != block_bytes_) {
+      munmap(block_, block_bytes_);
+      throw std::runtime_error("shared memory segment " + shm_name + " was created for a different configuration");
+    }
+  }
+}
+
+ShmCluster::~ShmCluster() {
+  if (block_ == nullptr) return;
+  if (shm_name_.empty()) {
+    std::free(block_);
+  } else {
+    munmap(block_, block_bytes_);
+    if (shm_owner_) shm_unlink(shm_name_.c_str());
+  }
+}
+
+int ShmCluster::issued(int rank) const {
+  if (rank < 0 || rank >= cfg_.world) throw std::invalid_argument("ShmCluster: rank out of range");
+  return next_round_[static_cast<size_t>(rank)].load();
 }
 
 int ShmCluster::next_round() const {

@@ -20,6 +20,7 @@
 #include <atomic>
 #include <cstdint>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "aar/device_layout.h"
@@ -68,7 +69,17 @@ struct ShmFreeRunStats {
 
 class ShmCluster {
  public:
-  explicit ShmCluster(const ShmConfig& cfg);
+  explicit ShmCluster(const ShmConfig& cfg);  // private memory: every rank is a thread of this process
+  // Named POSIX shared memory: one process per rank, like the reference's one JVM per worker.  `create` makes (and on
+  // destruction unlinks) the segment; the others attach, wait for it to be initialised and check that it was made
+  // for the same configuration.
+  // A segment whose creator process is gone is a leftover of an earlier run with the same name: an attacher keeps
+  // waiting for the new one unless `accept_orphan` (a replacement joining a job whose creator has died).
+  ShmCluster(const ShmConfig& cfg, const std::string& shm_name, bool create, double attach_timeout_s = 30.0,
+             bool accept_orphan = false);
+  ~ShmCluster();
+  ShmCluster(const ShmCluster&) = delete;
+  ShmCluster& operator=(const ShmCluster&) = delete;
 
   // One rank's round (tag = round + 1): returns when that rank has completed it.  One caller thread per rank;
   // a rank issues its rounds in increasing order.
@@ -84,6 +95,7 @@ class ShmCluster {
   // Rounds continue after the last one issued on this cluster.
   ShmFreeRunStats run_free(int rounds, double stall_prob, int stall_us, uint64_t seed);
   int next_round() const;  // lowest round number no rank has issued yet
+  int issued(int rank) const;  // lowest round number `rank` may still issue
 
   void force_complete(int rank, int round);  // waits of rounds <= `round` on `rank` close immediately
   const SymLayout& layout() const { return sym_; }
@@ -93,20 +105,26 @@ class ShmCluster {
   int total_chunks() const { return total_chunks_; }
 
  private:
-  struct AlignedFree {
-    void operator()(uint8_t* p) const;
-  };
-  uint8_t* region(int rank) const { return regions_[static_cast<size_t>(rank)].get(); }
+  void init_geometry();
+  void place(uint8_t* block);  // carve control words and regions out of one zero-filled block
+  static size_t control_bytes();
+  size_t region_bytes() const;
+  uint8_t* region(int rank) const { return regions_[static_cast<size_t>(rank)]; }
 
   ShmConfig cfg_;
   SymLayout sym_;
   Partition part_;
-  int L_, req_reduce_, req_complete_, gate_count_, total_chunks_;
-  std::vector<std::unique_ptr<uint8_t, AlignedFree>> regions_;
-  std::unique_ptr<std::atomic<uint32_t>[]> force_;     // per rank
-  std::unique_ptr<std::atomic<int>[]> progress_;       // per rank: round it is working on (free-run catch-up)
-  std::unique_ptr<std::atomic<int>[]> next_round_;     // per rank: lowest round it may still issue (tags never repeat)
-  std::unique_ptr<std::atomic<uint32_t>[]> notice_;    // [dest][src]: highest tag for which src left dest out
+  int L_ = 1, req_reduce_ = 0, req_complete_ = 0, gate_count_ = 0, total_chunks_ = 0;
+  uint8_t* block_ = nullptr;     // control words + world regions, malloc'ed or mmap'ed
+  size_t block_bytes_ = 0;
+  std::string shm_name_;         // empty: private memory
+  bool shm_owner_ = false;
+  std::vector<uint8_t*> regions_;
+  // control words (inside block_, so that processes attached to the same segment share them)
+  std::atomic<uint32_t>* force_ = nullptr;     // [rank]
+  std::atomic<int>* progress_ = nullptr;       // [rank]: round it is working on (free-run catch-up)
+  std::atomic<int>* next_round_ = nullptr;     // [rank]: lowest round it may still issue (tags never repeat)
+  std::atomic<uint32_t>* notice_ = nullptr;    // [dest][src]: highest tag for which src left dest out
 };
 
 }  // namespace aar
