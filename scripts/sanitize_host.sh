@@ -12,7 +12,7 @@ set -u
 cd "$(dirname "$0")/.."
 SANS=("$@"); [ ${#SANS[@]} -eq 0 ] && SANS=(address thread)
 CORE="csrc/host/buffers.cc csrc/host/worker_engine.cc csrc/host/master_engine.cc csrc/host/local_bus.cc csrc/host/node.cc"
-TESTS="tests/test_protocol_spec.py tests/test_buffers.py tests/test_master_and_cluster.py tests/test_chaos_cpu.py tests/test_config_cli_tcp.py tests/test_shm_cluster.py"
+TESTS="tests/test_protocol_spec.py tests/test_buffers.py tests/test_master_and_cluster.py tests/test_chaos_cpu.py tests/test_config_cli_tcp.py tests/test_shm_cluster.py tests/test_shm_worker.py"
 PATTERN='WARNING: ThreadSanitizer|ERROR: AddressSanitizer|runtime error:|ERROR: LeakSanitizer'
 mkdir -p build_san
 status=0
