@@ -169,8 +169,29 @@ void TcpNode::stop() {
     if (thread_.joinable() && std::this_thread::get_id() != thread_.get_id()) thread_.join();
     running_.store(false);
   }
+  // Orderly close.  close() on a socket that still has UNREAD input makes the kernel send a reset instead of a FIN,
+  // and a reset lets the peer's stack throw away what it has received from us but not yet read — e.g. the last
+  // completion reports of a worker that leaves while StartAllreduce frames it never looked at are still queued.
+  // So: half-close (our data, then FIN), read and discard until the peer closes too or a short grace period ends.
   for (auto& [id, c] : conns_)
-    if (c.fd >= 0) close(c.fd);
+    if (c.fd >= 0) shutdown(c.fd, SHUT_WR);
+  const auto grace_end = Clock::now() + std::chrono::milliseconds(300);
+  for (auto& [id, c] : conns_) {
+    if (c.fd < 0) continue;
+    const int fl = fcntl(c.fd, F_GETFL, 0);
+    fcntl(c.fd, F_SETFL, fl | O_NONBLOCK);
+    uint8_t sink[4096];
+    for (;;) {
+      const ssize_t got = ::read(c.fd, sink, sizeof(sink));
+      if (got > 0) continue;
+      if (got == 0 || (errno != EAGAIN && errno != EWOULDBLOCK && errno != EINTR)) break;  // peer closed / error
+      const auto left = std::chrono::duration_cast<std::chrono::milliseconds>(grace_end - Clock::now()).count();
+      if (left <= 0) break;
+      pollfd pf{c.fd, POLLIN, 0};
+      poll(&pf, 1, static_cast<int>(left));
+    }
+    close(c.fd);
+  }
   conns_.clear();
   if (listen_fd_ >= 0) {
     close(listen_fd_);

@@ -401,3 +401,43 @@ def test_handler_mode_worker_node_drives_the_coordinator():
         for n in nodes:
             n.stop()
         master.stop()
+
+
+def test_reports_survive_a_worker_that_leaves_with_unread_input():
+    """Workers that gate rounds themselves run ahead of the coordinator and may leave the moment their last report is
+    queued — with StartAllreduce frames they never read still in their socket.  A plain close() then answers with a
+    reset, and a reset lets the coordinator's stack drop reports it had received but not yet read (seen as a
+    coordinator stuck a few rounds before the end, once in ~15 runs).  stop() half-closes and drains instead."""
+    from akka_allreduce_b200 import host
+
+    rounds = 1500
+    for attempt in range(4):
+        cfg = _cluster(3, 16, 4, rounds)
+        master = AllreduceMaster(cfg)
+        port = master.start()
+        nodes = []
+        for _ in range(3):
+            node = host.WorkerNode("127.0.0.1", port, None, None, host.WorkerNodeOptions())
+            st = {"id": -1, "sent": False}
+
+            def on_message(msg, node=node, st=st):
+                if isinstance(msg, host.InitWorkers) and st["id"] < 0:
+                    st["id"] = msg.dest_id
+                elif isinstance(msg, host.StartAllreduce) and not st["sent"] and st["id"] >= 0:
+                    st["sent"] = True
+                    for r in range(rounds + 1):          # free-running worker: every report at once ...
+                        node.report_complete(st["id"], r)
+
+            node.set_handler(on_message)
+            node.listen("127.0.0.1", 0)
+            node.begin()
+            nodes.append((node, st))
+        try:
+            t0 = time.time()
+            while not all(st["sent"] for _, st in nodes) and time.time() - t0 < 20:
+                time.sleep(0.001)
+            for node, _ in nodes:                         # ... and gone, without reading what the coordinator sends
+                node.stop()
+            assert master.wait(30.0), f"attempt {attempt}: coordinator stuck at round {master.round} of {rounds}"
+        finally:
+            master.stop()
