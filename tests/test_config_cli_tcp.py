@@ -267,6 +267,12 @@ def test_quickstart_example_runs():
     assert p.returncode == 0 and p.stdout.strip().startswith("ok:"), p.stdout[-500:] + p.stderr[-1500:]
 
 
+def test_shm_quickstart_example_runs():
+    p = subprocess.run([sys.executable, os.path.join(ROOT, "examples", "quickstart_shm.py")], capture_output=True,
+                       text=True, timeout=120, env=dict(os.environ, PYTHONPATH=ROOT))
+    assert p.returncode == 0 and p.stdout.strip().startswith("ok:"), p.stdout[-500:] + p.stderr[-1500:]
+
+
 def test_native_cpu_cluster_binary():
     """The host runtime stands alone: coordinator + workers in one native process (no Python in the loop),
     reference defaults (2 workers, dataSize 10, maxChunkSize 2, th 1/1/0.8) and the 4-worker manual config with
