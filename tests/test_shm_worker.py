@@ -121,3 +121,52 @@ def test_shm_backend_cli_processes():
     for w, o in zip(ws, outs):
         assert w.returncode == 0, o
         assert "MBytes/sec" in o and "----Data output at #200" in o and "assertion failed" not in o
+
+
+def test_shm_backend_replacement_worker_rejoins():
+    """Elastic path on shared memory: one of 4 workers leaves, a replacement registers, the coordinator hands it the
+    vacated id and the current round, it attaches to the running job's segment and continues after its predecessor's
+    last round tag; all four contribute again afterwards."""
+    P, n = 4, 64
+    cfg = _cfg(P, n, 8, 600, th=(0.75, 0.75, 0.75), max_lag=2, timeout_ms=200.0)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    name = f"/aar_test_{os.getpid()}_rejoin"
+    seen = {}
+
+    def make(tag, value):
+        def source(req):
+            time.sleep(0.0005)                       # keep the job running long enough to leave and come back
+            return AllReduceInput(np.full(n, value, dtype=np.float32))
+
+        def sink(out, tag=tag):
+            seen.setdefault(tag, []).append((out.iteration, int(np.array(out.count).max())))
+
+        w = create_worker(source, sink, cfg, master_port=port, shm_name=name)
+        w.start()
+        return w
+
+    workers = [make(i, 1.0) for i in range(P)]
+    try:
+        t0 = time.time()
+        while master.round < 30 and time.time() - t0 < 20:
+            time.sleep(0.002)
+        victim = next(w for w in workers if w.id not in (-1, 0))     # not the segment's creator
+        vid = victim.id
+        victim.stop()
+        t0 = time.time()
+        while master.alive != 3 and time.time() - t0 < 10:
+            time.sleep(0.005)
+        assert master.alive == 3
+        repl = make("replacement", 1.0)
+        workers.append(repl)
+        assert master.wait(60), f"master stuck at round {master.round}"
+        assert repl.id == vid and master.alive == 4
+    finally:
+        for w in workers:
+            w.stop()
+        master.stop()
+    rounds = [r for r, _ in seen["replacement"]]
+    assert rounds and min(rounds) >= 30
+    survivor = next(i for i in range(P) if seen.get(i) and workers[i] is not victim)
+    assert any(c == 4 for r, c in seen[survivor] if r > min(rounds) + 5)      # everybody is counted again
