@@ -128,7 +128,7 @@ def test_shm_backend_replacement_worker_rejoins():
     vacated id and the current round, it attaches to the running job's segment and continues after its predecessor's
     last round tag; all four contribute again afterwards."""
     P, n = 4, 64
-    cfg = _cfg(P, n, 8, 600, th=(0.75, 0.75, 0.75), max_lag=2, timeout_ms=200.0)
+    cfg = _cfg(P, n, 8, 2000, th=(0.75, 0.75, 0.75), max_lag=2, timeout_ms=200.0)
     master = AllreduceMaster(cfg)
     port = master.start()
     name = f"/aar_test_{os.getpid()}_rejoin"
@@ -136,7 +136,7 @@ def test_shm_backend_replacement_worker_rejoins():
 
     def make(tag, value):
         def source(req):
-            time.sleep(0.0005)                       # keep the job running long enough to leave and come back
+            time.sleep(0.001)                        # >= 2 s of job: time to leave and come back, even on a busy box
             return AllReduceInput(np.full(n, value, dtype=np.float32))
 
         def sink(out, tag=tag):
