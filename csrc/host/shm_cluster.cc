@@ -1,5 +1,6 @@
 #include "shm_cluster.h"
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -45,9 +46,6 @@ inline void relax(int& spins) {
   }
 }
 
-}  // namespace
-
-namespace {
 struct ShmHeader {  // first words of a shared segment
   uint32_t magic, ready;
   int32_t world, max_lag;
@@ -198,6 +196,8 @@ int ShmCluster::next_round() const {
 }
 
 void ShmCluster::force_complete(int rank, int round) {
+  if (rank < 0 || rank >= cfg_.world) throw std::invalid_argument("ShmCluster: rank out of range");
+  if (round < 0) return;
   auto& f = force_[static_cast<size_t>(rank)];
   uint32_t want = static_cast<uint32_t>(round) + 1u, cur = f.load();
   while (cur < want && !f.compare_exchange_weak(cur, want)) {
