@@ -319,8 +319,9 @@ ShmRoundInfo ShmCluster::rank_round(int rank, int round, const float* src, float
         std::fill(acc.begin(), acc.begin() + len, 0.f);
         for (int s = 0; s < P; ++s) {  // peer order, like the reference's reduce (ScatteredDataBuffer.scala:20-30)
           if (!((have >> s) & 1u)) continue;
-          const float* r = rows + sym_.scat_elem(slot, s) + cb;
-          for (int64_t k = 0; k < len; ++k) acc[static_cast<size_t>(k)] += r[k];
+          const float* __restrict r = rows + sym_.scat_elem(slot, s) + cb;
+          float* __restrict a = acc.data();
+          for (int64_t k = 0; k < len; ++k) a[k] += r[k];
         }
         if (cfg_.normalize && cnt > 0) {
           const float post = 1.f / static_cast<float>(cnt);
