@@ -79,3 +79,53 @@ class AllreduceCommHook:
             eng.close()
         self._engines.clear()
         self._outs.clear()
+
+
+class ShmAllreduceCommHook:
+    """The same hook for CPU data parallelism on one host: gradient buckets are averaged by the device protocol in
+    POSIX shared memory (``host.ShmCluster``) instead of the fused kernel over NVLink.
+
+    DDP itself still needs a process group for its own bookkeeping (``gloo``); the gradient traffic does not go
+    through it.  One shared segment per bucket size, created by rank 0 and attached by the others on first use (every
+    rank meets the same bucket sizes in the same order).  The call blocks until this rank's round is complete — there
+    is no second stream to overlap with on a CPU — and returns an already-completed future.  fp32 on the wire.
+
+        model = DDP(model)                                   # CPU tensors, gloo process group
+        model.register_comm_hook(None, ShmAllreduceCommHook(rank, world, name="/job42"))
+    """
+
+    def __init__(self, rank: int, world: int, name: str, max_chunk_bytes: int = 1 << 18, max_lag: int = 1,
+                 th_reduce: float = 1.0, th_complete: float = 1.0, timeout_ms: float = 30_000.0):
+        self.rank, self.world, self.name = rank, world, name
+        self.__name__ = self.__qualname__ = "akka_allreduce_b200_shm_allreduce_hook"
+        self.max_chunk_bytes, self.max_lag = max_chunk_bytes, max_lag
+        self.th_reduce, self.th_complete, self.timeout_ms = th_reduce, th_complete, timeout_ms
+        self._clusters: Dict[int, Tuple[object, int]] = {}   # numel -> (cluster, next round)
+        self.buckets_reduced = 0
+
+    def _cluster(self, numel: int):
+        entry = self._clusters.get(numel)
+        if entry is None:
+            from .. import host
+
+            c = host.ShmConfig()
+            c.world, c.n, c.max_chunk, c.max_lag = self.world, numel, max(1, self.max_chunk_bytes // 4), self.max_lag
+            c.th_reduce, c.th_complete, c.th_allreduce = self.th_reduce, self.th_complete, 1.0
+            c.timeout_ms, c.normalize = self.timeout_ms, True       # mean over the contributors, like the kernel
+            entry = (host.ShmCluster.attach(c, f"{self.name}_{numel}", self.rank == 0), 0)
+        return entry
+
+    def __call__(self, state, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+        buf = bucket.buffer()
+        cluster, round_ = self._cluster(buf.numel())
+        src = buf.detach().to(torch.float32).contiguous().numpy()
+        out, _counts, _info = cluster.rank_round(self.rank, round_, src)
+        self._clusters[buf.numel()] = (cluster, round_ + 1)
+        buf.copy_(torch.from_numpy(out).to(buf.dtype))
+        self.buckets_reduced += 1
+        fut: torch.futures.Future[torch.Tensor] = torch.futures.Future()
+        fut.set_result(buf)
+        return fut
+
+    def close(self) -> None:
+        self._clusters.clear()   # unmaps the segments (rank 0 unlinks them)
