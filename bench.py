@@ -145,7 +145,11 @@ def main() -> int:
     value = algbw * world
     busbw = algbw * 2 * (world - 1) / world
 
-    extras = {"busbw_GBps": round(busbw, 2), "algbw_per_rank_GBps": round(algbw, 2), "correct": ok,
+    try:
+        roof = roofline(world, eng.algo, msg_bytes, ms, zero_copy, os.path.join(ROOT, "MEASURED_PEAKS.json"))
+    except Exception as ex:  # bookkeeping never takes the headline down
+        roof = {"error": str(ex)[:200]}
+    extras = {"busbw_GBps": round(busbw, 2), "algbw_per_rank_GBps": round(algbw, 2), "roofline": roof, "correct": ok,
               "max_rel_err": err, "multicast": eng.has_multicast, "algo": eng.algo, "ctas": eng.launcher.ctas,
               "zero_copy_buffers": zero_copy,
               "timeouts": eng.timeouts_seen()}
@@ -221,6 +225,39 @@ def main() -> int:
         dist.barrier()
         dist.destroy_process_group()
     return 0 if ok else 1
+
+
+def roofline(world: int, algo: str, msg_bytes: int, ms: float, zero_copy: bool, peaks_path: str) -> dict:
+    """Fraction of the roofline of the variant that actually ran.  One GPU: the round is HBM traffic only (the
+    single contribution is read and written once, the counts written once, plus the staging/flush copies when the
+    tensors are not the slots themselves), against the MEASURED copy bandwidth in MEASURED_PEAKS.json.  Several GPUs:
+    NVLink bus bandwidth against 900 GB/s per direction nominal — B for unicast two-shot, B x 2(P-1)/(P+1) for the
+    in-switch (NVLS) variant, and per-GPU ingress (P-1) x N for one-shot."""
+    out = {}
+    t = ms * 1e-3
+    if world == 1:
+        hbm = None
+        try:
+            with open(peaks_path) as f:
+                hbm = float(json.load(f)["hbm_gbs"])
+        except Exception:
+            pass
+        moved = msg_bytes * (3 if zero_copy else 7)   # slots: r + w + counts; user tensors: + stage (r+w) + flush (r+w)
+        out = {"bound": "HBM", "bytes_per_step": moved, "achieved_GBps": round(moved / t / 1e9, 1),
+               "peak_GBps": hbm, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if hbm else "unavailable",
+               "fraction": round(moved / t / 1e9 / hbm, 3) if hbm else None}
+    else:
+        link = 900.0
+        busbw = msg_bytes / t / 1e9 * 2 * (world - 1) / world
+        if algo == "nvls":
+            peak = link * 2 * (world - 1) / (world + 1)
+        elif algo == "oneshot":
+            peak = link * 2 / world      # ingress (P-1) x N at link rate, expressed as bus bandwidth
+        else:
+            peak = link
+        out = {"bound": "NVLink", "variant": algo, "busbw_GBps": round(busbw, 1), "roofline_busbw_GBps": round(peak, 1),
+               "peak_source": "900 GB/s per direction nominal", "fraction": round(busbw / peak, 3)}
+    return out
 
 
 def run_e2e(rank, world, local, n, mc, W, S, max_over_ranks, barrier):

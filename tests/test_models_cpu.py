@@ -62,3 +62,27 @@ def test_numa_placement_helpers(tmp_path, monkeypatch):
     monkeypatch.delenv("AAR_NO_AFFINITY")
     monkeypatch.setattr(A, "pci_address", lambda i: None)
     assert A.bind_to_gpu(0, str(tmp_path)) is None
+
+
+def test_bench_roofline_bookkeeping(tmp_path):
+    """bench.py's roofline fractions: HBM-bound on one GPU (against the measured copy bandwidth), NVLink-bound beyond
+    (B, B x 2(P-1)/(P+1) for the in-switch variant, B x 2/P for one-shot)."""
+    import json
+    import os
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    import bench
+
+    peaks = tmp_path / "peaks.json"
+    peaks.write_text(json.dumps({"hbm_gbs": 6000.0}))
+    n = 64 << 20
+    r = bench.roofline(1, "twoshot", n, 0.0865, True, str(peaks))
+    assert r["bound"] == "HBM" and r["bytes_per_step"] == 3 * n and abs(r["fraction"] - 3 * n / 86.5e-6 / 1e9 / 6000) < 1e-3
+    assert bench.roofline(1, "twoshot", n, 0.123, False, str(peaks))["bytes_per_step"] == 7 * n
+    assert bench.roofline(1, "twoshot", n, 0.1, True, str(tmp_path / "missing.json"))["fraction"] is None
+    r = bench.roofline(8, "nvls", n, 0.2047, True, str(peaks))
+    assert r["roofline_busbw_GBps"] == 1400.0 and abs(r["busbw_GBps"] - 573.7) < 1.0 and abs(r["fraction"] - 0.41) < 0.01
+    assert bench.roofline(2, "twoshot", n, 0.135, True, str(peaks))["roofline_busbw_GBps"] == 900.0
+    assert bench.roofline(8, "oneshot", 1 << 20, 0.02, True, str(peaks))["roofline_busbw_GBps"] == 225.0
