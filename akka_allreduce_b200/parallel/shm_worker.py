@@ -133,6 +133,11 @@ class ShmWorker:
         # the coordinator says where the job ends (InitWorkers.max_round); an older coordinator leaves it to the config
         n, last = sc.n, (init.max_round if init.max_round >= 0 else cfg.data.maxRound)
         r = max(init.start_round, cl.issued(self.id))  # a replacement continues after its predecessor's last round
+        if joining_late:
+            # ... and not behind the job: the coordinator's round is already history by the time this process has
+            # attached, and a worker that starts behind stays behind (thresholds below 1 do not wait for it).  The
+            # segment knows where the front-runner is; starting there, the gate lets the others catch up with us.
+            r = max(r, cl.next_round)
         self.round = r
         while r <= last:
             with self._cv:

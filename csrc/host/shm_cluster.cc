@@ -113,8 +113,13 @@ ShmCluster::ShmCluster(const ShmConfig& cfg, const std::string& shm_name, bool c
     shm_unlink(shm_name.c_str());  // a stale segment of a crashed run
     fd = shm_open(shm_name.c_str(), O_CREAT | O_EXCL | O_RDWR, 0600);
     if (fd < 0) throw std::runtime_error("shm_open(" + shm_name + ", create): " + std::strerror(errno));
-    if (ftruncate(fd, static_cast<off_t>(block_bytes_)) != 0) {
-      const std::string why = std::strerror(errno);
+    // posix_fallocate reserves the pages now: a /dev/shm that is too small (64 MB by default in containers) is an
+    // error message here instead of a SIGBUS at the first store into the region
+    int rc = ftruncate(fd, static_cast<off_t>(block_bytes_)) != 0 ? errno : 0;
+    if (rc == 0) rc = posix_fallocate(fd, 0, static_cast<off_t>(block_bytes_));
+    if (rc != 0) {
+      const std::string why = std::string(std::strerror(rc)) + " (" + std::to_string(block_bytes_ >> 20) +
+                              " MiB of shared memory needed: world x (maxLag+1) x 2 x message bytes)";
       close(fd);
       shm_unlink(shm_name.c_str());
       throw std::runtime_error("ftruncate(" + shm_name + "): " + why);

@@ -125,8 +125,8 @@ def test_shm_backend_cli_processes():
 
 def test_shm_backend_replacement_worker_rejoins():
     """Elastic path on shared memory: one of 4 workers leaves, a replacement registers, the coordinator hands it the
-    vacated id and the current round, it attaches to the running job's segment and continues after its predecessor's
-    last round tag; all four contribute again afterwards."""
+    vacated id and the current round, it attaches to the running job's segment, starts at the job's front and
+    contributes again: worker i sends 2^i, so the sums the survivors receive show the vacated id's bit coming back."""
     P, n = 4, 64
     cfg = _cfg(P, n, 8, 2000, th=(0.75, 0.75, 0.75), max_lag=2, timeout_ms=200.0)
     master = AllreduceMaster(cfg)
@@ -134,19 +134,25 @@ def test_shm_backend_replacement_worker_rejoins():
     name = f"/aar_test_{os.getpid()}_rejoin"
     seen = {}
 
-    def make(tag, value):
+    def make(tag):
+        box = {}
+
         def source(req):
             time.sleep(0.001)                        # >= 2 s of job: time to leave and come back, even on a busy box
-            return AllReduceInput(np.full(n, value, dtype=np.float32))
+            return AllReduceInput(np.full(n, float(1 << box["w"].id), dtype=np.float32))
 
         def sink(out, tag=tag):
-            seen.setdefault(tag, []).append((out.iteration, int(np.array(out.count).max())))
+            bits = 0
+            for v in np.unique(np.array(out.data)):
+                bits |= int(v)
+            seen.setdefault(tag, []).append((out.iteration, bits))
 
         w = create_worker(source, sink, cfg, master_port=port, shm_name=name)
+        box["w"] = w
         w.start()
         return w
 
-    workers = [make(i, 1.0) for i in range(P)]
+    workers = [make(i) for i in range(P)]
     try:
         t0 = time.time()
         while master.round < 30 and time.time() - t0 < 20:
@@ -158,7 +164,7 @@ def test_shm_backend_replacement_worker_rejoins():
         while master.alive != 3 and time.time() - t0 < 10:
             time.sleep(0.005)
         assert master.alive == 3
-        repl = make("replacement", 1.0)
+        repl = make("replacement")
         workers.append(repl)
         assert master.wait(60), f"master stuck at round {master.round}"
         assert repl.id == vid and master.alive == 4
@@ -169,4 +175,6 @@ def test_shm_backend_replacement_worker_rejoins():
     rounds = [r for r, _ in seen["replacement"]]
     assert rounds and min(rounds) >= 30
     survivor = next(i for i in range(P) if seen.get(i) and workers[i] is not victim)
-    assert any(c == 4 for r, c in seen[survivor] if r > min(rounds) + 5)      # everybody is counted again
+    gone = [r for r, bits in seen[survivor] if not bits & (1 << vid)]
+    back = [r for r, bits in seen[survivor] if r > min(rounds) and bits & (1 << vid)]
+    assert gone and back, (len(gone), len(back))          # its contribution stopped, then came back
