@@ -151,3 +151,25 @@ def test_scale_and_normalize_like_the_kernel():
     assert np.isin(counts[0], (3, 4)).all() and np.allclose(outs[0][full], 0.5 * 10 / 4)
     three = {round(0.5 * (10 - v) / 3, 5) for v in (1, 2, 3, 4)}        # whichever rank was not waited for
     assert all(round(float(x), 5) in three for x in outs[0][~full])
+
+
+def test_any_shape_matches_plain_sums():
+    """Property test over the geometry: any (world, n, maxChunkSize, maxLag), including n < world (empty blocks),
+    chunks larger than blocks and prime sizes — the region layout and the partition arithmetic are the kernel's own
+    headers, so this also walks `SymLayout` / `Partition` through shapes the fixed cases do not reach."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.integers(1, 9), st.integers(1, 700), st.integers(1, 97), st.integers(0, 3), st.integers(0, 2 ** 31))
+    def run(world, n, mc, lag, seed):
+        cl = make(world, n, mc, lag, timeout_ms=10000.0)
+        rng = np.random.default_rng(seed)
+        for rnd in range(lag + 2):
+            srcs = [rng.integers(-50, 50, n).astype(np.float32) for _ in range(world)]      # exact in fp32
+            outs, counts, infos = cl.run_round(rnd, srcs)
+            want = np.sum(srcs, axis=0, dtype=np.float32)
+            for r in range(world):
+                assert np.array_equal(outs[r], want) and (counts[r] == world).all(), (world, n, mc, lag, rnd, r)
+                assert not infos[r]["timed_out"]
+
+    run()
