@@ -68,3 +68,18 @@ def test_in_place_round_is_refused_below_full_thresholds():
         eng.allreduce(big[:64], big[32:])          # partial overlap counts too
     eng.launcher.req_reduce = 4
     assert not eng.partial_thresholds
+
+
+@pytest.mark.parametrize("n,mc,P,lag", [(10, 2, 2, 1), (778, 3, 4, 3), (9, 2, 4, 1), (1 << 20, 1 << 16, 8, 1), (100003, 4096, 5, 2)])
+def test_shared_memory_cluster_uses_the_kernels_region_layout(n, mc, P, lag):
+    """host.ShmCluster (CPU threads) and libaar_cuda (the kernel) size one rank's symmetric region from the same
+    header: same bytes, same thresholds, same chunk totals."""
+    lib = K.lib()
+    c = host.ShmConfig()
+    c.world, c.n, c.max_chunk, c.max_lag = P, n, mc, lag
+    c.th_reduce, c.th_complete = 0.75, 0.8
+    cl = host.ShmCluster(c)
+    assert cl.region_bytes == lib.aar_sym_bytes(n, mc, P, lag + 1, K.F32, 0, 0)
+    geo = Geometry.make(n, mc, P, lag, False)
+    assert (cl.total_chunks, cl.req_reduce, cl.req_complete) == (geo.total_chunks, geo.req_reduce(0.75), geo.req_complete(0.8))
+    assert cl.gate_count == gate_count(1.0, P)
