@@ -322,7 +322,10 @@ if __name__ == "__main__":
     t0 = time.time()
     r = check(cfg, walks=a.walks, seed=a.seed)
     print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")
-    if not r.ok:
-        print("  " + r.violation)
-        for step in (r.trace or [])[-40:]:
-            print("    " + step)
+    try:
+        if not r.ok:
+            print("  " + r.violation)
+            for step in (r.trace or [])[-40:]:
+                print("    " + step)
+    except BrokenPipeError:  # `... | head`
+        pass
