@@ -8,7 +8,8 @@ by the snapshot):
 * ``libaar_cuda.so``  - sm_100a CUDA kernels + symmetric heap behind a C ABI
                         (``include/aar_b200.h``), built with nvcc, loaded through ctypes.
 
-``python -m akka_allreduce_b200.build`` builds both; ``--host`` / ``--cuda`` pick one.
+``python -m akka_allreduce_b200.build`` builds both; ``--host`` / ``--cuda`` pick one; ``--tools`` builds the
+stand-alone binaries ``build/aar_cpu_cluster`` and ``build/aar_shm_cluster``.
 Rebuilds only when a source or header is newer than the artefact.
 """
 from __future__ import annotations
@@ -243,3 +244,6 @@ if __name__ == "__main__":
         print(build_host(force))
     if "--cuda" in args or not (args - {"--force"}):
         print(build_cuda(force))
+    if "--tools" in args:  # stand-alone native binaries: TCP cluster and shared-memory cluster
+        print(build_cpu_cluster(force))
+        print(build_shm_cluster(force))
