@@ -51,6 +51,7 @@ class ClusterConfig:
     downAfter: float = 10.0    # seconds (auto-down-unreachable-after = 10s)
     heartbeat: float = 1.0
     loglevel: str = "INFO"
+    metricsPort: int = 0       # > 0: the master serves Prometheus metrics on this port (utils/metrics.py)
 
 
 @dataclass

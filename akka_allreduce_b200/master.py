@@ -30,6 +30,7 @@ class AllreduceMaster:
         opts.verbose = verbose
         self._node = host.MasterNode(config.master_config(), opts)
         self.port = None
+        self.metrics = None
 
     def start(self) -> int:
         c = self.config
@@ -37,13 +38,32 @@ class AllreduceMaster:
         self.log.info("-------\n Port = %s \n Number of Workers = %s \n Message Size = %s \n Max Chunk Size = %s",
                       self.port, c.worker.totalSize, c.data.dataSize, c.data.maxChunkSize)
         self._node.start()
+        if c.cluster.metricsPort > 0:
+            self.serve_metrics(c.cluster.metricsPort)
         return self.port
+
+    def serve_metrics(self, port: int = 0) -> int:
+        """Prometheus endpoint with the coordinator's view of the job; returns the port (0 = any free one)."""
+        from .utils.metrics import MetricsExporter
+
+        def collect():
+            return {"aar_master_round": self.round, "aar_master_alive_workers": self.alive,
+                    "aar_master_registered_workers": self.registered,
+                    "aar_master_total_workers": self.config.worker.totalSize,
+                    "aar_master_max_round": self.config.data.maxRound,
+                    "aar_master_finished": 1.0 if self._node.wait_finished(0.0) else 0.0}
+
+        self.metrics = MetricsExporter(collect, port, self.config.cluster.host, {"role": "master"})
+        return self.metrics.port
 
     def wait(self, timeout: float = 3600.0) -> bool:
         """Blocks until round ``maxRound`` has passed the gate (or the timeout expires)."""
         return self._node.wait_finished(timeout)
 
     def stop(self) -> None:
+        if self.metrics is not None:
+            self.metrics.close()
+            self.metrics = None
         self._node.stop()
 
     round = property(lambda self: self._node.round)

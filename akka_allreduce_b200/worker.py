@@ -108,6 +108,25 @@ def create_worker(data_source: DataSource, data_sink: DataSink, config: Allreduc
                            loglevel=config.cluster.loglevel, **kwargs)
 
 
+def serve_worker_metrics(worker, port: int = 0, host_: str = "127.0.0.1"):
+    """Prometheus endpoint for any of the three worker kinds (they share `id`, `rounds_completed` and, with the
+    built-in sink, `stats`).  Returns the exporter (`.port`, `.close()`)."""
+    from .utils.metrics import MetricsExporter
+
+    def collect():
+        m = {"aar_worker_id": worker.id, "aar_worker_rounds_completed": worker.rounds_completed}
+        stats = getattr(worker, "stats", None)
+        if stats is not None:
+            m["aar_worker_checkpoints"] = stats.checkpoints
+            m["aar_worker_sink_assertion_failures"] = stats.failures
+            m["aar_worker_mbytes_per_s"] = stats.last_mbytes_per_s
+        if hasattr(worker, "timeouts"):
+            m["aar_worker_round_timeouts"] = worker.timeouts
+        return m
+
+    return MetricsExporter(collect, port, host_, {"role": "worker"})
+
+
 def ramp_source(data_size: int) -> DataSource:
     floats = np.arange(data_size, dtype=np.float32)
     return lambda req: AllReduceInput(floats)
@@ -143,6 +162,7 @@ def main(argv: list[str] | None = None) -> int:
     ap.add_argument("--checkpoint", type=int)
     ap.add_argument("--assert-multiple", type=int)
     ap.add_argument("--backend", choices=["cpu", "shm", "cuda"])
+    ap.add_argument("--metrics-port", type=int, default=0, help="serve Prometheus metrics of this worker on this port")
     a = ap.parse_args(sys.argv[1:] if argv is None else argv)
     # like the reference, whose application.conf is picked up without being named: the checkout's (or the
     # packaged) application.conf is read unless --config / AAR_CONFIG names another file
@@ -153,11 +173,14 @@ def main(argv: list[str] | None = None) -> int:
                  a.assert_multiple if a.assert_multiple is not None else cfg.worker.assertMultiple,
                  a.master_host or cfg.cluster.host, a.master_port or cfg.cluster.port,
                  a.backend or cfg.device.backend, cfg)
+    exporter = serve_worker_metrics(w, a.metrics_port) if a.metrics_port > 0 else None
     try:
         w.wait()
     except KeyboardInterrupt:
         pass
     finally:
+        if exporter is not None:
+            exporter.close()
         w.stop()
     fails = w.stats.failures if getattr(w, "stats", None) is not None else 0
     return 1 if fails else 0

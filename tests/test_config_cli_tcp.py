@@ -447,3 +447,44 @@ def test_reports_survive_a_worker_that_leaves_with_unread_input():
             assert master.wait(30.0), f"attempt {attempt}: coordinator stuck at round {master.round} of {rounds}"
         finally:
             master.stop()
+
+
+def test_prometheus_metrics_of_master_and_worker():
+    """Observability beyond the reference's printed MBytes/sec (its cluster-metrics extension is loaded and never
+    read): the coordinator and any worker can be scraped."""
+    import urllib.request
+
+    from akka_allreduce_b200.utils.metrics import render
+    from akka_allreduce_b200.worker import serve_worker_metrics
+
+    assert render({"aar_x": 3}, {"role": "master"}) == '# TYPE aar_x gauge\naar_x{role="master"} 3\n'
+    cfg = _cluster(2, 16, 4, 30)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    mport = master.serve_metrics(0)
+    workers = [AllreduceWorker.builtin(16, checkpoint=10, assert_multiple=2, master_port=port) for _ in range(2)]
+    exporters = []
+    try:
+        for w in workers:
+            w.start()
+            exporters.append(serve_worker_metrics(w))
+        assert master.wait(30)
+
+        def scrape(p):
+            text = urllib.request.urlopen(f"http://127.0.0.1:{p}/metrics", timeout=5).read().decode()
+            return {l.split("{")[0]: float(l.rsplit(" ", 1)[1]) for l in text.splitlines() if l and not l.startswith("#")}
+
+        m = scrape(mport)
+        assert m["aar_master_round"] == 30 and m["aar_master_finished"] == 1 and m["aar_master_total_workers"] == 2
+        ws = [scrape(e.port) for e in exporters]
+        assert sorted(w["aar_worker_id"] for w in ws) == [0, 1]
+        assert all(w["aar_worker_rounds_completed"] == 31 and w["aar_worker_sink_assertion_failures"] == 0 for w in ws)
+        assert all(w["aar_worker_checkpoints"] == 3 for w in ws)
+        with pytest.raises(Exception):
+            urllib.request.urlopen(f"http://127.0.0.1:{mport}/nope", timeout=5)
+    finally:
+        for e in exporters:
+            e.close()
+        for w in workers:
+            w.stop()
+        master.stop()
