@@ -15,6 +15,7 @@ keys, ``=`` or ``:``, ``#``/``//`` comments, quoted or bare strings, lists, dura
 from __future__ import annotations
 
 import json
+import os
 import re
 from dataclasses import dataclass, field, asdict
 from pathlib import Path
@@ -99,7 +100,7 @@ _TOKEN = re.compile(
         (?P<comment>(?:\#|//)[^\n]*) |
         (?P<brace>[{}\[\],=:]) |
         "(?P<qstr>(?:[^"\\]|\\.)*)" |
-        (?P<bare>[^\s{}\[\],=:"#]+)
+        (?P<bare>(?:\$\{[^}\n]*\}|[^\s{}\[\],=:"#$])+)
     )""",
     re.X,
 )
@@ -107,7 +108,25 @@ _DURATION = re.compile(r"^(-?\d+(?:\.\d+)?)(ms|s|m|h)$")
 _UNITS = {"ms": 1e-3, "s": 1.0, "m": 60.0, "h": 3600.0}
 
 
+_SUBST = re.compile(r"\$\{([^}]*)\}")
+
+
+def _substitute(tok: str) -> str:
+    """``${name}`` as in HOCON: environment variables, plus the JVM properties the reference's file uses."""
+    def value(m):
+        name = m.group(1).lstrip("?")
+        if name == "user.dir":
+            return os.getcwd()
+        if name == "user.home":
+            return os.path.expanduser("~")
+        return os.environ.get(name, m.group(0))
+
+    return _SUBST.sub(value, tok)
+
+
 def _scalar(tok: str) -> Any:
+    if "${" in tok:
+        tok = _substitute(tok)
     low = tok.lower()
     if low in ("true", "on", "yes"):
         return True
@@ -262,6 +281,12 @@ def _apply(cfg: AllreduceConfig, tree: dict) -> None:
                 cfg.cluster.host = str(tcp["hostname"])
             if isinstance(val, dict) and "loglevel" in val:
                 cfg.cluster.loglevel = str(val["loglevel"])
+            seeds = val.get("cluster", {}).get("seed-nodes") if isinstance(val, dict) else None
+            if seeds and not tcp.get("port"):
+                # the first seed node is where the reference's master listens (akka.tcp://ClusterSystem@host:2551)
+                m = re.search(r"@([^:/]+):(\d+)", str(seeds[0]))
+                if m:
+                    cfg.cluster.host, cfg.cluster.port = m.group(1), int(m.group(2))
             down = val.get("cluster", {}).get("auto-down-unreachable-after") if isinstance(val, dict) else None
             if down is not None:
                 cfg.cluster.downAfter = float(down)
