@@ -28,7 +28,11 @@ class AllreduceMaster:
         opts = host.MasterNodeOptions()
         opts.down_after_s = config.cluster.downAfter
         opts.verbose = verbose
-        self._node = host.MasterNode(config.master_config(), opts)
+        mc = config.master_config()
+        # GPU workers must be told when a peer is gone (they would push into and wait on a dead process's memory);
+        # the CPU backends keep the reference's behaviour (stale peers become dead letters) unless asked
+        mc.announce_removals = config.cluster.announceRemovals or config.device.backend == "cuda"
+        self._node = host.MasterNode(mc, opts)
         self.port = None
         self.metrics = None
 

@@ -14,6 +14,8 @@ MAX_RANKS = 16
 F32, BF16 = 0, 1
 ALGO_TWOSHOT, ALGO_ONESHOT, ALGO_NVLS = 0, 1, 2
 ALGO_NAMES = {"twoshot": ALGO_TWOSHOT, "oneshot": ALGO_ONESHOT, "nvls": ALGO_NVLS}
+KERNEL_AUTO, KERNEL_GENERIC, KERNEL_STREAM = 0, 1, 2
+KERNEL_NAMES = {"auto": KERNEL_AUTO, "generic": KERNEL_GENERIC, "stream": KERNEL_STREAM}
 
 
 class AarLaunch(C.Structure):
@@ -24,6 +26,7 @@ class AarLaunch(C.Structure):
         ("algo", C.c_int32), ("in_dtype", C.c_int32), ("wire_dtype", C.c_int32),
         ("ctas", C.c_int32), ("use_tma", C.c_int32), ("fast_fences", C.c_int32),
         ("role_s", C.c_int32), ("role_c", C.c_int32), ("nvls_unroll", C.c_int32), ("part_kb", C.c_int32), ("overlap_flush", C.c_int32), ("oneshot_pull", C.c_int32),
+        ("kernel", C.c_int32), ("mc_bcast", C.c_int32),
         ("n", C.c_int64), ("max_chunk", C.c_int64), ("os_cap", C.c_int64), ("block_step", C.c_int64),
         ("L", C.c_int32), ("slot", C.c_int32),
         ("tag", C.c_uint32),
@@ -73,14 +76,20 @@ def lib() -> C.CDLL:
         fn.argtypes = [i64, i64, i32, i32, i32, i64, i64]
     l.aar_scratch_bytes.restype = i64
     l.aar_scratch_bytes.argtypes = [i64, i64, i32, i64]
-    l.aar_scratch_force_offset.restype = i64
-    l.aar_scratch_force_offset.argtypes = [i64, i64, i32, i64]
+    for fn in (l.aar_scratch_force_offset, l.aar_scratch_dead_offset):
+        fn.restype = i64
+        fn.argtypes = [i64, i64, i32, i64]
     l.aar_allreduce_round.restype = i32
     l.aar_allreduce_round.argtypes = [C.POINTER(AarLaunch), vp]
     l.aar_allreduce_round_static_scratch.restype = i32
     l.aar_allreduce_round_static_scratch.argtypes = [C.POINTER(AarLaunch), vp]
     l.aar_max_emu_ctas.restype = i32
     l.aar_max_emu_ctas.argtypes = [i32, i32]
+    l.aar_max_ctas.restype = i32
+    l.aar_max_ctas.argtypes = [i32, i32, i32]
+    for fn in (l.aar_round_kernel, l.aar_round_ctas):
+        fn.restype = i32
+        fn.argtypes = [C.POINTER(AarLaunch)]
     l.aar_heap_create.restype = i32
     l.aar_heap_create.argtypes = [C.POINTER(vp), i32, i32, i32, i64, C.c_char_p, i32]
     l.aar_heap_ptrs.restype = i32

@@ -33,15 +33,15 @@ class Injection:
 
 class RoundLauncher:
     def __init__(self, geo: Geometry, dtype: torch.dtype, wire_dtype: torch.dtype, th_reduce: float,
-                 th_complete: float, th_allreduce: float | None, ctas: int, timeout_ms: float,
-                 scale: float = 1.0, normalize: bool = False, os_cap: int = 0, algo: int = K.ALGO_TWOSHOT):
+                 th_complete: float, th_allreduce: float | None, ctas: int | None, timeout_ms: float,
+                 scale: float = 1.0, normalize: bool = False, os_cap: int = 0, algo: int = K.ALGO_TWOSHOT,
+                 kernel: str | None = None):
         self.lib = K.lib()
         self.geo = geo
         self.dtype, self.wire_dtype = dtype, wire_dtype
         self.in_code, self.wire_code = K.dtype_code(dtype), K.dtype_code(wire_dtype)
         self.os_cap = os_cap
         self.algo = algo
-        self.ctas = ctas
         self.timeout_ns = int(timeout_ms * 1e6)
         self.scale, self.normalize = scale, normalize
         self.req_reduce = geo.req_reduce(th_reduce)
@@ -64,7 +64,20 @@ class RoundLauncher:
         self.off_sink = self.lib.aar_sym_sink_offset(*layout_args)
         self.scratch_bytes = self.lib.aar_scratch_bytes(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
         self.force_offset = self.lib.aar_scratch_force_offset(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
+        self.dead_offset = self.lib.aar_scratch_dead_offset(geo.n, geo.max_chunk, geo.world, geo.block_step_arg)
+        # Which two-shot kernel: "auto" = the stream kernel (warp tiles, two CTAs per SM) whenever the launch is
+        # 16-byte aligned and needs no dtype conversion, else the generic one.  AAR_KERNEL=generic|stream forces it.
+        self.kernel = K.KERNEL_NAMES[kernel or os.environ.get("AAR_KERNEL", "auto")]
+        # ReduceBlock broadcast through the multicast alias (one multimem.st per 16 bytes instead of P stores)
+        # on the two-shot push path; NVLS always broadcasts that way.  AAR_MC_BCAST=1.
+        self.mc_bcast = int(os.environ.get("AAR_MC_BCAST", 0))
         self.launches = 0
+        # the stream kernel needs 16-byte aligned block starts and chunk starts (and aligned tensors, checked per launch)
+        align = 16 // min(torch.empty((), dtype=dtype).element_size(), torch.empty((), dtype=wire_dtype).element_size())
+        self.stream_expected = (self.kernel != K.KERNEL_GENERIC and dtype == wire_dtype and geo.step % align == 0
+                                and (geo.max_chunk % align == 0 or geo.max_chunk >= geo.step))
+        # work CTAs per rank; the library clamps it to what the device keeps resident (aar_max_ctas)
+        self.ctas = ctas or default_ctas(geo.n * torch.empty((), dtype=dtype).element_size(), self.stream_expected)
         # one-shot flavour: 0 push (default), 1 pull with in-switch reduce, 2 pull with unicast loads (opt-in:
         # written after the round's multi-GPU budget was spent, validated in emulation only — see DESIGN.md 7)
         self.oneshot_pull = int(os.environ.get("AAR_ONESHOT_PULL", 0))
@@ -84,13 +97,14 @@ class RoundLauncher:
         ov = os.environ.get("AAR_OVERLAP")
         a.overlap_flush = int(ov) if ov in ("0", "1") else (1 if g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20) else 0)
         a.oneshot_pull = self.oneshot_pull
+        a.kernel, a.mc_bcast = self.kernel, self.mc_bcast
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))
         # largest work item: 256 KB, 64 KB for messages of 512 MB and more (measured on 8 GPUs at 1 GB: 64 KB
         # 2.93 ms, 256 KB 3.01 ms, 1 MB 3.11 ms — smaller windows keep the pages in flight within TLB reach)
         big = g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20)
-        a.part_kb = int(os.environ.get("AAR_PART_KB", 64 if big else 0))
+        a.part_kb = int(os.environ.get("AAR_PART_KB", 64 if (big and not self.stream_expected) else 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate
@@ -136,20 +150,22 @@ class EmulatedCluster:
                  wire_dtype=None, th_reduce: float = 1.0, th_complete: float = 1.0,
                  th_allreduce: float | None = None, ctas: int | None = None, align_blocks: bool = False,
                  timeout_ms: float = 2000.0, scale: float = 1.0, normalize: bool = False,
-                 device: str | torch.device = "cuda:0", algo: str = "twoshot"):
+                 device: str | torch.device = "cuda:0", algo: str = "twoshot", kernel: str | None = None):
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
         wire = wire_dtype or dtype
         lib = K.lib()
-        cap = K.check(lib.aar_max_emu_ctas(world, self.device.index or 0), "aar_max_emu_ctas")
-        want = ctas or default_ctas(n * torch.empty((), dtype=dtype).element_size())
         if algo not in ("twoshot", "oneshot"):
             raise ValueError("the emulated cluster runs the two-shot and one-shot kernels (NVLS needs real peers)")
         self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
-                                      max(1, min(want, cap)), timeout_ms, scale, normalize,
-                                      os_cap=n if algo == "oneshot" else 0, algo=K.ALGO_NAMES[algo])
+                                      ctas, timeout_ms, scale, normalize,
+                                      os_cap=n if algo == "oneshot" else 0, algo=K.ALGO_NAMES[algo], kernel=kernel)
         L = self.launcher
+        # all ranks share this GPU: (ctas + 1) x world CTAs must be resident at once
+        cap = K.check(lib.aar_max_ctas(K.KERNEL_STREAM if L.stream_expected else K.KERNEL_GENERIC, world,
+                                       self.device.index or 0), "aar_max_ctas")
+        L.ctas = max(1, min(L.ctas, cap))
         self.world = world
         self.sym = torch.zeros(world, L.sym_bytes, dtype=torch.uint8, device=self.device)
         self.scratch = torch.zeros(world, L.scratch_bytes, dtype=torch.uint8, device=self.device)
@@ -189,6 +205,25 @@ class EmulatedCluster:
         if round_ is None:
             self.round += 1
         return outs, counts
+
+    def set_dead_peers(self, masks: dict) -> None:
+        """rank -> bit mask of the peers that rank is told are dead (the host-written word of its scratch)."""
+        off = self.launcher.dead_offset
+        for r in range(self.world):
+            self.scratch[r, off:off + 4].view(torch.int32).fill_(int(masks.get(r, 0)))
+
+    def kernel_used(self) -> str:
+        """Which kernel the library picks for this cluster's launches: generic | stream | oneshot."""
+        return {1: "generic", 2: "stream", 3: "oneshot"}[K.check(self.lib_kernel_query(), "aar_round_kernel")]
+
+    def lib_kernel_query(self) -> int:
+        a = self._a
+        self.launcher.fill(a, self.round, None)
+        for i in range(self.world):
+            a.src[i] = a.src[i] or self.outs[i].data_ptr()
+            a.out[i] = self.outs[i].data_ptr()
+            a.counts[i] = self.counts[i].data_ptr()
+        return self.launcher.lib.aar_round_kernel(C.byref(a))
 
     def timeouts_seen(self) -> list[int]:
         torch.cuda.synchronize(self.device)

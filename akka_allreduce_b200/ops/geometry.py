@@ -80,7 +80,20 @@ class Geometry:
                 yield o, c, self.start(o) + min(c * self.max_chunk, b), self.start(o) + min((c + 1) * self.max_chunk, b)
 
 
-def default_ctas(message_bytes: int) -> int:
+def default_ctas(message_bytes: int, stream: bool = False) -> int:
+    """Work CTAs per rank.  The generic kernel holds one 512-thread CTA per SM, the stream kernel two (its unit of
+    work is a warp tile, so it wants about one warp per 2-32 KB of the largest phase); the library clamps the
+    number to what the device keeps resident."""
+    if stream:
+        if message_bytes <= 64 << 10:
+            return 4
+        if message_bytes <= 1 << 20:
+            return 16
+        if message_bytes <= 4 << 20:
+            return 64
+        if message_bytes <= 16 << 20:
+            return 128
+        return 512
     if message_bytes <= 64 << 10:
         return 4
     if message_bytes <= 1 << 20:

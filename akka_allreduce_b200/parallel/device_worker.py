@@ -62,6 +62,7 @@ class DeviceWorker:
         self._cv = threading.Condition()
         self._init = None
         self._start_round = -1
+        self._dead_mask = 0
         self._stop = False
         self._thread = None
         self._error = None
@@ -77,8 +78,18 @@ class DeviceWorker:
     def _on_message(self, msg) -> None:
         with self._cv:
             if isinstance(msg, host.InitWorkers):
-                if self._init is None:  # later InitWorkers only refresh the peer map (AllreduceWorker.scala:87-89)
+                if self._init is None:
                     self._init = msg
+                # later InitWorkers only refresh the peer map (AllreduceWorker.scala:87-89): ids that are no longer
+                # in it belong to workers the master has removed (AllreduceMaster.scala:46-52).  On the GPU that
+                # becomes the kernels' dead-peer mask: no pushes to them, no waiting for them.  Membership of the
+                # symmetric heap is fixed, so a removed id stays dead for the rest of the job.
+                alive = set(msg.workers.keys())
+                for q in range(msg.worker_num):
+                    if q not in alive and q != msg.dest_id:
+                        self._dead_mask |= 1 << q
+                if self.engine is not None and self._dead_mask:
+                    self.engine.set_dead_peers(self._dead_mask)
             elif isinstance(msg, host.StartAllreduce):
                 self._start_round = max(self._start_round, msg.round)
                 eng = self.engine
@@ -136,8 +147,9 @@ class DeviceWorker:
             self.device_index = int(local) if local is not None else self.id % torch.cuda.device_count()
         torch.cuda.set_device(self.device_index)
         placement = bind_to_gpu(self.device_index)  # this thread and the ones it starts: cores next to the GPU
-        if placement:
-            self.log.info("----bound to NUMA node %d (%d cpus)", placement["numa_node"], placement["cpus"])
+        if placement and placement.get("bound"):
+            self.log.info("----bound to the %d cpus next to cuda:%d (NUMA node %s, from %s)", placement["cpus"],
+                          self.device_index, placement.get("numa_node"), placement.get("source"))
         dtype = _DTYPES[dev_cfg.dtype]
         gate_on_device = dev_cfg.gate == "device"
         self.engine = DeviceAllreduce(
@@ -149,6 +161,9 @@ class DeviceWorker:
             scale=dev_cfg.scale, normalize=dev_cfg.normalize, algo=dev_cfg.algo)
         eng = self.engine
         dev = eng.device
+        with self._cv:
+            if self._dead_mask:  # a peer was removed while the heap was coming up
+                eng.set_dead_peers(self._dead_mask)
         self.log.info("----Actor id = %d on cuda:%d; peers = %d; thReduce = %s, thComplete = %s, maxLag = %d; "
                       "symmetric region %.1f MiB, multicast %s", self.id, self.device_index, world, init.th_reduce,
                       init.th_complete, init.max_lag, eng.launcher.sym_bytes / 2 ** 20, eng.has_multicast)

@@ -50,7 +50,7 @@ class DeviceAllreduce:
                  th_reduce: float = 1.0, th_complete: float = 1.0, th_allreduce: float | None = None,
                  device: int | None = None, uds_dir: str | None = None, multicast: bool = True,
                  align_blocks: bool = True, ctas: int | None = None, timeout_ms: float = 2000.0,
-                 scale: float = 1.0, normalize: bool = False, algo: str = "auto"):
+                 scale: float = 1.0, normalize: bool = False, algo: str = "auto", kernel: str | None = None):
         self.rank, self.world = rank, world
         self.device_index = torch.cuda.current_device() if device is None else device
         self.device = torch.device("cuda", self.device_index)
@@ -69,9 +69,12 @@ class DeviceAllreduce:
             raise K.AarError("algo=oneshot needs thReduce = thComplete = 1 and maxLag >= 1 (or the thAllreduce gate)")
         use_oneshot = algo == "oneshot" or (algo == "auto" and oneshot_ok and small and world > 1)
         self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
-                                      ctas or default_ctas(n * elem), timeout_ms, scale, normalize,
-                                      os_cap=n if use_oneshot else 0)
+                                      ctas, timeout_ms, scale, normalize, os_cap=n if use_oneshot else 0, kernel=kernel)
         lib = self.launcher.lib
+        # every CTA of a launch must be resident: the generic kernel fits one per SM, the stream kernel two
+        cap = K.check(lib.aar_max_ctas(K.KERNEL_STREAM if self.launcher.stream_expected else K.KERNEL_GENERIC, 1,
+                                       self.device_index), "aar_max_ctas")
+        self.launcher.ctas = max(1, min(self.launcher.ctas, cap))
         self._heap = C.c_void_p()
         K.check(lib.aar_heap_create(C.byref(self._heap), rank, world, self.device_index, self.launcher.sym_bytes,
                                     (uds_dir or default_uds_dir()).encode(), int(multicast)), "aar_heap_create")
@@ -100,6 +103,9 @@ class DeviceAllreduce:
         off = self.launcher.force_offset
         self._force_word = self.scratch[off:off + 4].view(torch.int32)      # device word the kernels poll
         self._force_src = torch.zeros(1, dtype=torch.int32).pin_memory()
+        off = self.launcher.dead_offset
+        self._dead_word = self.scratch[off:off + 4].view(torch.int32)       # bit q: peer q is known dead
+        self._dead_src = torch.zeros(1, dtype=torch.int32).pin_memory()
         self._ctl_stream = torch.cuda.Stream(device=self.device)
         self.round = 0
         self._launch = a = K.AarLaunch()
@@ -132,9 +138,14 @@ class DeviceAllreduce:
 
     def input_view(self, round_: int) -> torch.Tensor | None:
         """Tensor aliasing the staging slot of ``round_`` (NVLS mode only: there the scatter stages the
-        message locally and the switch pulls it).  A source written here needs no copy at all."""
+        message locally and the switch pulls it).  A source written here needs no copy at all.
+        Only handed out when both data thresholds are 1: the caller writes the slot outside the launch, i.e. past
+        the kernel's back-pressure, and the only thing that keeps a slow owner from still reading round r - L out of
+        it is that this rank could not have finished r - L without that owner's chunks (thComplete = 1)."""
         # (push mode stages nothing locally — except with a single rank, whose own scat row IS the staging slot)
         if not (self.zero_copy_ok and (self.algo == "nvls" or self.world == 1)):
+            return None
+        if self.partial_thresholds:
             return None
         l, g = self.launcher, self.geo
         esz = torch.empty((), dtype=l.wire_dtype).element_size()
@@ -202,7 +213,7 @@ class DeviceAllreduce:
         t0 = float(t[:, 0].min())
         us = lambda x: round(float(x) / 1e3, 1)
         out = {"gate_us": us((t[:, 1] - t0).max()), "end_us": us((t[:, 4] - t0).max())}
-        for role, name, col in ((0, "all", 4), (1, "S", 2), (2, "R", 3), (3, "C", 4)):
+        for role, name, col in ((0, "all", 4), (1, "S", 2), (2, "R", 3), (3, "C", 4), (4, "stream", 4)):
             rows = t[t[:, 8] == role]
             if len(rows) == 0:
                 continue
@@ -211,6 +222,12 @@ class DeviceAllreduce:
                 entry["wait_us"] = [us(rows[:, 5].min()), us(rows[:, 5].max())]
             if role in (0, 3):
                 entry["wait_c_us"] = [us(rows[:, 6].min()), us(rows[:, 6].max())]
+            if role == 4:
+                entry["wait_us"] = [us(rows[:, 5].min()), us(rows[:, 5].max())]
+                entry["wait_c_us"] = [us(rows[:, 6].min()), us(rows[:, 6].max())]
+                first = rows[:, 2][rows[:, 2] > 0]
+                if len(first):
+                    entry["first_reduce_us"] = [us((first - t0).min()), us((first - t0).max())]
             if role == 0:
                 entry["S_done_us"] = [us((rows[:, 2] - t0).min()), us((rows[:, 2] - t0).max())]
                 entry["R_done_us"] = [us((rows[:, 3] - t0).min()), us((rows[:, 3] - t0).max())]
@@ -227,6 +244,23 @@ class DeviceAllreduce:
         self._force_src[0] = round_ + 1
         with torch.cuda.stream(self._ctl_stream):
             self._force_word.copy_(self._force_src, non_blocking=True)
+
+    def set_dead_peers(self, mask: int) -> None:
+        """Peers the coordinator reported gone (bit q = rank q): the kernels stop pushing to them and stop waiting
+        for them — they count as absent contributors (AllreduceMaster.scala:46-52, AllreduceWorker.scala:213-216).
+        Travels like the force tag: a 4-byte async copy that also reaches a kernel that is already waiting."""
+        mask &= ~(1 << self.rank)
+        if int(self._dead_src[0]) == mask:
+            return
+        self._ctl_stream.synchronize()
+        self._dead_src[0] = mask
+        with torch.cuda.stream(self._ctl_stream):
+            self._dead_word.copy_(self._dead_src, non_blocking=True)
+        # (the NVLS kernel needs no switch: a dead peer never raises a flag, so every chunk takes the unicast path)
+
+    @property
+    def dead_peers(self) -> int:
+        return int(self._dead_src[0])
 
     def last_done_round(self) -> int:
         return int(self.host_flags[1]) - 1

@@ -6,8 +6,9 @@ inter-socket link on every H2D copy (and the coordinator/worker threads pay it o
 the process to the GPU's NUMA node before it allocates anything keeps buffers, threads and PCIe root on one side.
 The reference leaves placement to the JVM and the OS; NCCL does the same thing for its own threads.
 
-Everything here is best effort: on a single-node host, in a container that hides sysfs, or with
-``AAR_NO_AFFINITY`` set, nothing happens.
+Everything here is best effort: the GPU's NUMA node comes from sysfs, or — in a container that hides it — from the
+CPU affinity NVML reports for the device; on a single-node host, or with ``AAR_NO_AFFINITY`` set, nothing is bound,
+and the returned record says why.
 """
 from __future__ import annotations
 
@@ -58,21 +59,55 @@ def pci_address(device_index: int) -> str | None:
         return None
 
 
+def nvml_cpus_of_gpu(device_index: int) -> set[int]:
+    """Cores NVML calls ideal for this GPU (what ``nvidia-smi topo -m`` prints as CPU affinity).  Works where the
+    container hides the PCI device's sysfs node; empty when NVML cannot say."""
+    try:
+        import pynvml as nv
+        import torch
+
+        nv.nvmlInit()
+        try:
+            p = torch.cuda.get_device_properties(device_index)
+            bus = f"{p.pci_domain_id:08x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+            handle = nv.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            words = (os.cpu_count() + 63) // 64
+            mask = nv.nvmlDeviceGetCpuAffinity(handle, words)
+            return {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+        finally:
+            nv.nvmlShutdown()
+    except Exception:
+        return set()
+
+
 def bind_to_gpu(device_index: int, sysfs: str = "/sys") -> dict | None:
-    """Restricts the calling thread (and every thread it starts later) to the cores of the GPU's NUMA node.
-    Returns what was done ({'numa_node': n, 'cpus': count}) or None when there was nothing to do."""
+    """Restricts the calling thread (and every thread it starts later) to the cores next to the GPU: the cores of
+    its NUMA node (sysfs), else the CPU affinity NVML reports for it.  Always says what happened:
+    ``{'bound': True, 'numa_node': n | None, 'cpus': count, 'source': 'sysfs' | 'nvml'}`` or
+    ``{'bound': False, 'reason': ...}``; None only when AAR_NO_AFFINITY is set or the platform has no affinity calls."""
     if os.environ.get("AAR_NO_AFFINITY") is not None or not hasattr(os, "sched_setaffinity"):
         return None
     addr = pci_address(device_index)
     node = numa_node_of_pci(addr, sysfs) if addr else None
-    if node is None:
-        return None
     try:
         allowed = os.sched_getaffinity(0)
-        local = cpus_of_node(node, sysfs) & allowed
-        if len(local) < MIN_LOCAL_CPUS or local == allowed:
-            return None  # nothing to gain, or too few local cores for the worker, IO and sampler threads
+    except OSError as e:
+        return {"bound": False, "reason": f"sched_getaffinity: {e}"}
+    local, source = set(), None
+    if node is not None:
+        local, source = cpus_of_node(node, sysfs) & allowed, "sysfs"
+    if not local:
+        local, source = nvml_cpus_of_gpu(device_index) & allowed, "nvml"
+    if not local:
+        return {"bound": False, "reason": "neither sysfs nor NVML names the cores next to this GPU",
+                "allowed_cpus": len(allowed)}
+    if local == allowed:
+        return {"bound": False, "reason": "the process is already confined to the GPU's cores", "numa_node": node,
+                "cpus": len(local), "source": source}
+    if len(local) < MIN_LOCAL_CPUS:  # too few local cores for the worker, IO and sampler threads
+        return {"bound": False, "reason": f"only {len(local)} local cores allowed", "numa_node": node, "source": source}
+    try:
         os.sched_setaffinity(0, local)
-    except OSError:
-        return None
-    return {"numa_node": node, "cpus": len(local)}
+    except OSError as e:
+        return {"bound": False, "reason": f"sched_setaffinity: {e}"}
+    return {"bound": True, "numa_node": node, "cpus": len(local), "source": source}

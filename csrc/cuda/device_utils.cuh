@@ -164,6 +164,14 @@ __device__ __forceinline__ void multimem_st(uint4* p, const uint4& v) {
                : "memory");
 }
 
+// Flag words through the multicast alias: one store lands in every rank's copy of the word.
+__device__ __forceinline__ void multimem_st_u32(uint32_t* p, uint32_t v) {
+  asm volatile("multimem.st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st_u64(uint64_t* p, uint64_t v) {
+  asm volatile("multimem.st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
 // ---------------------------------------------------------------- mbarrier + TMA bulk (1-D)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 

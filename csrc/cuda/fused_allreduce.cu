@@ -31,59 +31,21 @@
 #include <stdio.h>
 
 #include <atomic>
+#include <map>
 #include <mutex>
+#include <utility>
 #include <string>
+#include <type_traits>
 
 #include "aar/device_layout.h"
 #include "aar_b200.h"
 #include "device_utils.cuh"
+#include "round_common.cuh"
+#include "stream_kernel.cuh"
 
 namespace aar {
 
-constexpr int kThreads = 512;
 constexpr int kUnitsPerThread = 4;
-
-struct KParams {
-  AarLaunch a;
-  SymLayout sym;
-  ScratchLayout scr;
-  Partition part;
-  int part_s, tpc_s;  // scatter/complete phases: elements per work item, items per full chunk
-  int part_r, tpc_r;  // reduce phase: elements per work item, items per full chunk
-  int part_c, tpc_c;  // complete phase
-  int n_s, n_r, n_c;  // work CTAs per role (scatter / reduce+broadcast / complete); 0,0,0 = every CTA does all three
-  int total_chunks;   // reduced chunks that exist this round (empty trailing blocks excluded)
-  int vec_ok;         // 16-byte paths usable (alignment of pointers, step and chunk size)
-};
-
-struct Ctx {
-  int rank, vr, P, slot;
-  uint32_t tag;
-  uint8_t* my_sym;
-  uint8_t* scratch;
-  volatile uint32_t* host;
-  const uint32_t* force;  // device word: rounds <= force-1 close their waits immediately (catch-up)
-  uint64_t deadline;
-};
-
-__device__ __forceinline__ void note_timeout(const Ctx& c) {
-  if (c.host != nullptr) c.host[2] = c.tag;  // last round closed by a timeout (plain store: host memory)
-}
-// The force word lives in DEVICE memory (the host updates it with an async copy): a kernel that polls
-// host memory over PCIe while it waits slows every system-scope fence on the GPU down by an order of
-// magnitude (measured: profiles/fence_probe.md).  Waiting loops still look at it, and at the timer,
-// only every kSlowPoll-th iteration.
-__device__ __forceinline__ bool forced(const Ctx& c) { return ld_volatile(c.force) >= c.tag; }
-constexpr int kSlowPoll = 16;
-__device__ __forceinline__ bool give_up(const Ctx& c, int& spins, uint64_t deadline) {
-  if ((++spins & (kSlowPoll - 1)) != 0) return false;
-  if (forced(c)) return true;
-  if (globaltimer_ns() > deadline) {
-    note_timeout(c);
-    return true;
-  }
-  return false;
-}
 
 // ---------------------------------------------------------------- tile movers
 // src (TIn, local) -> dst (TW, possibly a peer), scaled.
@@ -128,7 +90,7 @@ __device__ __forceinline__ void push_tile(const TIn* __restrict__ src, TW* __res
 // whatever the peer count; every element is still accumulated in peer order 0..P-1.
 template <typename TW, int B>
 __device__ __forceinline__ void reduce_units(const TW* const* __restrict__ rows, uint32_t mask, int P,
-                                             TW* const* __restrict__ dst, int ndst, int units, float post) {
+                                             TW* const* __restrict__ dst, int ndst, TW* mc_dst, int units, float post) {
   constexpr int E = 16 / sizeof(TW);
   constexpr int PB = 8 / B;
   using U = Unit<TW, E>;
@@ -168,7 +130,9 @@ __device__ __forceinline__ void reduce_units(const TW* const* __restrict__ rows,
 #pragma unroll
         for (int e = 0; e < E; ++e) acc[b][e] *= post;
         const raw_t out = U::pack(acc[b]);
-        for (int q = 0; q < ndst; ++q) reinterpret_cast<raw_t*>(dst[q])[u] = out;
+        if (mc_dst != nullptr) multimem_st(reinterpret_cast<uint4*>(mc_dst) + u, out);  // one store, the switch replicates it
+        else
+          for (int q = 0; q < ndst; ++q) reinterpret_cast<raw_t*>(dst[q])[u] = out;
       }
     }
   }
@@ -176,15 +140,15 @@ __device__ __forceinline__ void reduce_units(const TW* const* __restrict__ rows,
 
 template <typename TW>
 __device__ __forceinline__ void reduce_tile(const TW* const* __restrict__ rows, uint32_t mask, int P,
-                                            TW* const* __restrict__ dst, int ndst, int len, float post, bool vec) {
+                                            TW* const* __restrict__ dst, int ndst, TW* mc_dst, int len, float post, bool vec) {
   constexpr int E = 16 / sizeof(TW);
   int done = 0;
   if (vec) {
     const int units = len / E;
     constexpr int BMAX = E == 8 ? 2 : 4;  // 8-wide units carry twice the accumulators
-    if (P <= 2) reduce_units<TW, BMAX>(rows, mask, P, dst, ndst, units, post);
-    else if (P <= 4) reduce_units<TW, 2>(rows, mask, P, dst, ndst, units, post);
-    else reduce_units<TW, 1>(rows, mask, P, dst, ndst, units, post);
+    if (P <= 2) reduce_units<TW, BMAX>(rows, mask, P, dst, ndst, mc_dst, units, post);
+    else if (P <= 4) reduce_units<TW, 2>(rows, mask, P, dst, ndst, mc_dst, units, post);
+    else reduce_units<TW, 1>(rows, mask, P, dst, ndst, mc_dst, units, post);
     done = units * E;
   }
   for (int i = done + threadIdx.x; i < len; i += kThreads) {
@@ -278,187 +242,6 @@ __device__ __forceinline__ void flush_tile(const TW* __restrict__ sink, TOut* __
       out[i] = present ? from_float<TOut>(to_float(ld_fresh_scalar(sink + i))) : from_float<TOut>(0.f);
       if (counts != nullptr) counts[i] = cnt;
     }
-  }
-}
-
-// ---------------------------------------------------------------- shared decisions
-// Set of peers this launch may push to: a peer whose ring slot still holds a round more than
-// maxLag behind is skipped for the whole launch (first CTA to look decides for all).
-__device__ __forceinline__ uint32_t decide_dest_mask(const KParams& p, const Ctx& c) {
-  uint32_t* word = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_fin_cnt) + 1;
-  uint32_t m = ld_volatile(word);
-  if (m & kDecided) return m & ~kDecided;
-  const uint32_t* done = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_done);
-  uint32_t ok = 0;
-  for (int q = 0; q < c.P; ++q) {
-    const uint32_t d = (q == c.rank) ? c.tag : ld_acquire_sys(done + q);
-    if (d + static_cast<uint32_t>(p.a.L) >= c.tag) ok |= 1u << q;
-  }
-  const uint32_t old = atomicCAS(word, 0u, ok | kDecided);
-  return (old & kDecided) ? (old & ~kDecided) : ok;
-}
-
-// thAllreduce gate: round r may start once `gate_count` peers have finished round r-1
-// (AllreduceMaster.scala:56-62, evaluated on every rank from the replicated `done` flags).
-__device__ __forceinline__ void wait_gate(const KParams& p, const Ctx& c) {
-  if (p.a.gate_count <= 0 || c.tag <= 1) return;
-  const uint32_t* done = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_done);
-  int spins = 0;
-  for (;;) {
-    int have = 0;
-    for (int q = 0; q < c.P; ++q) have += (q == c.rank || ld_volatile(done + q) + 1 >= c.tag) ? 1 : 0;
-    if (have >= p.a.gate_count) break;
-    if (give_up(c, spins, c.deadline)) return;
-    __nanosleep(64);
-  }
-  __threadfence();  // acquire side of the peers' CompleteAllreduce
-}
-
-// All CTAs of a rank report here; the last one resets the scratch and publishes completion.
-__device__ __forceinline__ void finish_cta(const KParams& p, const Ctx& c) {
-  uint32_t* fin = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_fin_cnt);
-  __threadfence();
-  const uint32_t old = atomicAdd(fin, 1u);
-  if (old != static_cast<uint32_t>(p.a.ctas) + 1u) return;  // ctas work CTAs + the two control warps
-  st_volatile(fin, 0u);
-  st_volatile(fin + 1, 0u);
-  st_volatile(fin + 3, 0u);  // (fin[2] is the host's force tag: not ours to reset)
-  uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
-  const int words = (c.P * p.sym.cpb + 31) / 32;
-  for (int i = 0; i < 4 + words; ++i) st_volatile(cw + i, 0u);
-  __threadfence();  // nothing but flags follows: the data of this round was fenced when its flags were raised
-  for (int i = 0; i < c.P; ++i) {  // CompleteAllreduce(rank, round) to everyone (AllreduceWorker.scala:276)
-    const int q = (i + c.rank) % c.P;
-    st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + c.rank, c.tag);
-  }
-  if (c.host != nullptr) c.host[1] = c.tag;
-}
-
-// ---------------------------------------------------------------- control CTA
-// Publisher warp: the only place flags leave this rank.  Data CTAs bump a local counter per
-// (destination, chunk) behind a gpu-scope fence — which, for stores that went to a peer, returns only
-// once the peer has acknowledged them; this warp polls the counters and raises the flags of every chunk
-// that has all its parts in: one scan, one fence, then all the flag stores.
-//
-// A system-scope fence on this machine waits for the NVLink traffic of the WHOLE GPU to drain (tens of
-// microseconds while a round is streaming; measured in profiles/fence_probe.md), which is why it is paid
-// here, once per batch, and never by a data CTA.  `fast_fences` (AAR_FAST_FENCES=1, experiments only)
-// downgrades it to gpu scope; that was observed to let a flag overtake multimem.st data on 8 GPUs.
-constexpr int kPubWords = 8;  // up to 256 (destination, chunk) + chunk entries per scan
-__device__ void publisher_warp(const KParams& p, const Ctx& c) {
-  const int lane = threadIdx.x & 31;
-  const int P = c.P, cpb = p.sym.cpb;
-  uint32_t* scat_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt);
-  uint32_t* red_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt);
-  uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask);
-  const uint32_t* fin = reinterpret_cast<const uint32_t*>(c.scratch + p.scr.off_fin_cnt);
-  const int s_entries = P * cpb;
-  const int entries = s_entries + cpb;
-  const int64_t my_bsize = p.part.size(c.rank);
-  bool last_pass = false;
-  for (;;) {
-    const bool closing = ld_volatile(fin + 3) >= static_cast<uint32_t>(p.a.ctas);  // read BEFORE the scan
-    for (int base0 = 0; base0 < entries; base0 += 32 * kPubWords) {
-      uint32_t mine = 0;  // bit w: entry base0 + 32*w + lane is complete and unpublished
-#pragma unroll
-      for (int w = 0; w < kPubWords; ++w) {
-        const int e = base0 + 32 * w + lane;
-        bool ready = false;
-        if (e < s_entries) {  // ScatterBlock (d, ch): all parts out?
-          const int d = e / cpb, ch = e % cpb;
-          const int64_t bs = p.part.size(d);
-          if (ch < num_chunks(bs, p.a.max_chunk)) {
-            const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s));
-            ready = ld_volatile(scat_cnt + e) == static_cast<uint32_t>(want);
-          }
-        } else if (e < entries) {  // ReduceBlock (me, ch): all parts reduced and broadcast?
-          const int ch = e - s_entries;
-          if (ch < num_chunks(my_bsize, p.a.max_chunk)) {
-            const int want = static_cast<int>(ceil_div(chunk_end(ch, p.a.max_chunk, my_bsize) - chunk_begin(ch, p.a.max_chunk, my_bsize), p.part_r));
-            ready = ld_volatile(red_cnt + ch) == static_cast<uint32_t>(want);
-          }
-        }
-        if (ready) mine |= 1u << w;
-      }
-      if (!__any_sync(0xffffffffu, mine != 0)) continue;
-      // Data that left this GPU (pushed scatter slices, broadcast results — unicast or multimem.st) must
-      // have landed on the peers before its flag does: that takes a system-scope fence.  Slices that were
-      // only staged locally (NVLS scatter) are ordered by a gpu-scope fence: the peers read them through
-      // this GPU's L2.
-      bool remote = false;
-#pragma unroll
-      for (int w = 0; w < kPubWords; ++w)
-        if ((mine >> w) & 1u) remote = remote || !(p.a.algo == AAR_ALGO_NVLS && base0 + 32 * w + lane < s_entries);
-      if (__any_sync(0xffffffffu, remote) && !p.a.fast_fences) __threadfence_system();
-      else __threadfence();
-#pragma unroll
-      for (int w = 0; w < kPubWords; ++w) {
-        if (!((mine >> w) & 1u)) continue;
-        const int e = base0 + 32 * w + lane;
-        if (e < s_entries) {
-          const int d = e / cpb, ch = e % cpb;
-          st_volatile(scat_cnt + e, 0u);
-          st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
-        } else {
-          const int ch = e - s_entries;
-          const uint32_t mask = ld_volatile(red_mask + ch) & ~kDecided;
-          const uint32_t dest_ok = ld_volatile(fin + 1) & ~kDecided;
-          st_volatile(red_cnt + ch, 0u);
-          st_volatile(red_mask + ch, 0u);
-          const uint64_t f = (static_cast<uint64_t>(c.tag) << 32) | static_cast<uint32_t>(__popc(mask));
-          for (int i = 0; i < P; ++i) {
-            const int q = (i + c.rank) % P;
-            if ((dest_ok >> q) & 1u)
-              st_relaxed_sys(reinterpret_cast<uint64_t*>(p.a.sym[q] + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
-          }
-        }
-      }
-    }
-    if (last_pass) break;
-    if (closing) last_pass = true;  // every work CTA is past phase R: one more scan picks up the rest
-    else __nanosleep(20);
-  }
-  if (lane == 0) finish_cta(p, c);
-}
-
-__device__ void control_cta(const KParams& p, const Ctx& c) {
-  if (threadIdx.x >= 64) return;
-  if (threadIdx.x >= 32) {
-    publisher_warp(p, c);
-    return;
-  }
-  const int lane = threadIdx.x;
-  const int cpb = p.sym.cpb;
-  const int entries = c.P * cpb;
-  const int words = (entries + 31) / 32;
-  const uint64_t* rflag = reinterpret_cast<const uint64_t*>(c.my_sym + p.sym.off_rflag) + (int64_t)c.slot * entries;
-  uint32_t* cw = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_complete);
-  uint32_t* bitmap = cw + 4;
-  int spins = 0;
-  for (;;) {
-    int seen = 0;
-    for (int w = 0; w < words; ++w) {
-      const int idx = w * 32 + lane;
-      bool present = false;
-      if (idx < entries) {
-        const int o = idx / cpb, ch = idx % cpb;
-        if (ch < num_chunks(p.part.size(o), p.a.max_chunk))
-          present = static_cast<uint32_t>(ld_volatile64(rflag + idx) >> 32) == c.tag;
-      }
-      const uint32_t m = __ballot_sync(0xffffffffu, present);
-      seen += __popc(m);
-      if (lane == 0 && m != 0) st_volatile(bitmap + w, m);
-    }
-    bool close = seen >= p.a.req_complete || seen >= p.total_chunks;
-    if (!close && lane == 0) close = give_up(c, spins, c.deadline + p.a.timeout_ns);  // owners get one timeout to
-    close = __shfl_sync(0xffffffffu, close ? 1 : 0, 0) != 0 || close;                 // reduce, the round one more
-    if (close) break;
-    __nanosleep(200);
-  }
-  if (lane == 0) {
-    __threadfence();
-    st_volatile(cw, kDecided);
-    finish_cta(p, c);
   }
 }
 
@@ -574,17 +357,23 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       fence_barrier_init();
     }
     sh_tile_cnt = -1;
-    if (p.a.delay_ns[c.rank] != 0) {  // injected straggler
+  }
+  if (threadIdx.x < 32) {  // gate, destination mask and skip notices: one lane per peer, one ballot each
+    if (threadIdx.x == 0 && p.a.delay_ns[c.rank] != 0) {  // injected straggler
       const uint64_t until = globaltimer_ns() + p.a.delay_ns[c.rank];
       while (globaltimer_ns() < until) __nanosleep(256);
     }
-    wait_gate(p, c);
-    sh_word = decide_dest_mask(p, c);
-    if (trace != nullptr) trace[1] = globaltimer_ns();
+    __syncwarp();
+    wait_gate_warp(p, c);
+    const uint32_t m = decide_dest_mask_warp(p, c);
+    if (threadIdx.x == 0) {
+      sh_word = m;
+      if (trace != nullptr) trace[1] = globaltimer_ns();
+    }
   }
   __syncthreads();
   const uint32_t dest_ok = sh_word;
-  const uint32_t all_ranks = P >= 32 ? 0xffffffffu : ((1u << P) - 1u);
+  const uint32_t all_ranks = all_ranks_mask(P);
   const bool muted = (p.a.mute_mask >> c.rank) & 1u;
   const uint32_t skip = p.a.skip_dest_mask[c.rank];
   __syncthreads();
@@ -595,13 +384,13 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   {
     const bool pure_copy = tma && sizeof(TIn) == sizeof(TW) && p.a.scale == 1.0f;
     const int tile = p.part_s, tpc = p.tpc_s;
-    const int items = do_s ? cpb * P * tpc : 0;
+    const int items = (do_s && !p.zc_src) ? cpb * P * tpc : 0;  // (zero-copy source: the publisher raised the flags at launch)
     for (int item = s_idx; item < items; item += s_stride) {
       const int k = item % tpc;
       const int d = ((item / tpc) % P + c.rank) % P;
       const int ch = item / (tpc * P);
       const int64_t bsize = p.part.size(d);
-      if (ch >= num_chunks(bsize, p.a.max_chunk)) continue;
+      if (ch >= p.nch[d]) continue;
       const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
       const int ntiles = static_cast<int>(ceil_div(ce - cb, tile));
       if (k >= ntiles) continue;
@@ -651,7 +440,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       o = ((c_item / c_tpc) % P + c.rank) % P;
       ch = c_item / (c_tpc * P);
       bsize = p.part.size(o);
-      if (ch >= num_chunks(bsize, p.a.max_chunk)) continue;
+      if (ch >= p.nch[o]) continue;
       cb = chunk_begin(ch, p.a.max_chunk, bsize);
       ce = chunk_end(ch, p.a.max_chunk, bsize);
       ntiles = static_cast<int>(ceil_div(ce - cb, c_tile));
@@ -682,10 +471,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
         __nanosleep(64);
       }
       int cnt = 0;
-      if (state == 1) {
-        cnt = static_cast<int>(static_cast<uint32_t>(ld_volatile64(rflag + idx)));
-        __threadfence();
-      }
+      if (state == 1) cnt = static_cast<int>(static_cast<uint32_t>(ld_acquire_sys(rflag + idx)));  // acquire: the owner's data
       sh_word = state;
       sh_cnt = cnt;
       if (trace != nullptr && blocking) wait_c += globaltimer_ns() - w0;
@@ -730,7 +516,7 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   // ---- phase R: reduce my block chunk by chunk and broadcast ----
   {
     const int64_t bsize = p.part.size(c.rank);
-    const int nch = num_chunks(bsize, p.a.max_chunk);
+    const int nch = p.nch[c.rank];
     const uint32_t* arr = reinterpret_cast<const uint32_t*>(c.my_sym + p.sym.off_arr) + p.sym.arr_index(c.slot, 0, 0);
     const int tile = p.part_r, tpc = p.tpc_r;
     const int items = do_r ? nch * tpc : 0;
@@ -742,27 +528,14 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
       if (k >= ntiles) continue;
       const int64_t off = cb + static_cast<int64_t>(k) * tile;
       const int len = static_cast<int>(min(static_cast<int64_t>(tile), ce - off));
-      if (threadIdx.x == 0) {
+      if (threadIdx.x < 32) {
         const uint64_t w0 = trace != nullptr ? globaltimer_ns() : 0;
-        uint32_t m = ld_volatile(red_mask + ch);
-        int spins = 0;
-        while (!(m & kDecided)) {
-          uint32_t have = 0;
-          for (int s = 0; s < P; ++s)
-            if (ld_volatile(arr + s * cpb + ch) == c.tag) have |= 1u << s;
-          if (__popc(have) >= p.a.req_reduce || give_up(c, spins, c.deadline)) {
-            // first CTA to see the threshold met (or to give up) fixes the contributor set of the chunk
-            const uint32_t old = atomicCAS(red_mask + ch, 0u, have | kDecided);
-            m = (old & kDecided) ? old : (have | kDecided);
-            break;
-          }
-          __nanosleep(100);
-          m = ld_volatile(red_mask + ch);
+        // first warp to see the threshold met (or nothing more to come, or to give up) fixes the contributor set
+        const uint32_t m = wait_chunk_mask(p, c, ch, threadIdx.x);
+        if (threadIdx.x == 0) {
+          sh_word = m;
+          if (trace != nullptr) wait_r += globaltimer_ns() - w0;
         }
-        m &= ~kDecided;
-        __threadfence();  // acquire side: the contributors' data is read from L2 / the switch, never from L1
-        sh_word = m;
-        if (trace != nullptr) wait_r += globaltimer_ns() - w0;
       }
       if (threadIdx.x < P) {
         const int q = (threadIdx.x + c.rank) % P;
@@ -789,7 +562,12 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
         else
           nvls_reduce_tile<TW, 8>(reinterpret_cast<const TW*>(p.a.mc_base + so), reinterpret_cast<TW*>(p.a.mc_base + to), len, post);
       } else {
-        reduce_tile<TW>(sh_rows, mask, P, sh_dst, P, len, post, vec);
+        // ReduceBlock to everyone: P unicast stores per unit, or (mc_bcast, NVLS alias present, nobody skipped) one
+        // multimem.st that the switch replicates — independent of how the sum was formed (AllreduceWorker.scala:252-268)
+        TW* mc_dst = nullptr;
+        if (p.a.mc_bcast && !p.a.emu && p.a.mc_base != nullptr && dest_ok == all_ranks && vec && len % EW == 0)
+          mc_dst = reinterpret_cast<TW*>(p.a.mc_base + p.sym.off_sink) + p.sym.sink_elem(c.slot, c.rank) + off;
+        reduce_tile<TW>(sh_rows, mask, P, sh_dst, P, mc_dst, len, post, vec);
       }
       __syncthreads();
       if (threadIdx.x == 0) {
@@ -858,23 +636,11 @@ template <typename TIn, typename TW, bool kPull>
 __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_constant__ KParams p) {
   __shared__ uint32_t sh_mask;
   __shared__ const TW* sh_rows[kMaxRanks];
-  const int vr = p.a.emu ? blockIdx.y : 0;
-  const int rank = p.a.emu ? static_cast<int>(blockIdx.y) : p.a.rank;
-  const int P = p.a.world, slot = p.a.slot;
-  const uint32_t tag = p.a.tag;
-  uint8_t* my_sym = p.a.sym[rank];
-  uint8_t* scratch = p.a.scratch[vr];
-  Ctx c;
-  c.rank = rank;
-  c.vr = vr;
-  c.P = P;
-  c.slot = slot;
-  c.tag = tag;
-  c.my_sym = my_sym;
-  c.scratch = scratch;
-  c.host = p.a.host_flags != nullptr ? p.a.host_flags + 4 * vr : nullptr;
-  c.force = reinterpret_cast<const uint32_t*>(scratch + p.scr.off_fin_cnt) + 2;
-  c.deadline = globaltimer_ns() + p.a.timeout_ns;
+  const Ctx c = make_ctx(p);
+  const int vr = c.vr, rank = c.rank, P = c.P, slot = c.slot;
+  const uint32_t tag = c.tag;
+  uint8_t* my_sym = c.my_sym;
+  uint8_t* scratch = c.scratch;
   const int nct = gridDim.x;
   const bool vec = p.vec_ok != 0;
   // slice of this CTA, in multiples of 8 elements so 16-byte accesses stay aligned
@@ -886,16 +652,37 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
   TIn* out = static_cast<TIn*>(p.a.out[vr]);
   int32_t* counts = p.a.counts[vr];
 
-  if (threadIdx.x == 0) {
-    if (p.a.delay_ns[rank] != 0) {
+  // Gate, destination mask and skip notices, as in the two-shot kernels (one lane per peer).  The mask is the
+  // device form of the reference's stale-round drop (AllreduceWorker.scala:172-173): a peer whose ring slot
+  // still holds a round more than maxLag behind gets nothing from this launch — a rank that gave up twice in a
+  // row must not overwrite a copy that a stalled peer is still summing — and is told so with a notice.
+  if (threadIdx.x < 32) {
+    if (threadIdx.x == 0 && p.a.delay_ns[rank] != 0) {
       const uint64_t until = globaltimer_ns() + p.a.delay_ns[rank];
       while (globaltimer_ns() < until) __nanosleep(256);
     }
-    wait_gate(p, c);
+    __syncwarp();
+    wait_gate_warp(p, c);
+    const uint32_t m = decide_dest_mask_warp(p, c);
+    if (threadIdx.x == 0) sh_mask = m;
   }
   __syncthreads();
-  const bool muted = (p.a.mute_mask >> rank) & 1u;
-  const uint32_t skip = p.a.skip_dest_mask[rank];
+  const uint32_t dest_ok = sh_mask;
+  const uint32_t all_ranks = all_ranks_mask(P);
+  bool muted = (p.a.mute_mask >> rank) & 1u;
+  if (kPull) {
+    // Pull form: peers read MY staging row, so the hazard is a lagging peer still reading the copy of round
+    // r - L that I am about to overwrite.  A mask cannot protect my own row; if anybody alive is that far
+    // behind I sit this round out instead (contribute nothing) and tell everyone not to wait for me.
+    const uint32_t dead = ld_volatile(fin_words(p, c) + 4);
+    if (((dest_ok | dead) & all_ranks) != all_ranks) {
+      muted = true;
+      if (threadIdx.x < P && static_cast<int>(threadIdx.x) != rank && !((dead >> threadIdx.x) & 1u))
+        st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[threadIdx.x] + p.sym.off_notice) + rank, tag);
+    }
+  }
+  __syncthreads();  // sh_mask is reused below
+  const uint32_t skip = p.a.skip_dest_mask[rank] | (~dest_ok & all_ranks);
 
   // ---- push my slice to every peer (self first) — or, pull form, stage it once locally — then raise my flag
   if (len > 0 && !muted) {
@@ -928,20 +715,27 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
   }
 
   // ---- wait for every sender's slice, then reduce locally
-  if (threadIdx.x == 0) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
     const uint32_t* arr = reinterpret_cast<const uint32_t*>(my_sym + p.sym.off_os_arr) +
                           static_cast<int64_t>(slot) * P * kMaxOneShotCtas + blockIdx.x;
-    const uint32_t all = (1u << P) - 1u;
     uint32_t have = 0;
     int spins = 0;
     for (;;) {
-      for (int s = 0; s < P; ++s)
-        if (!((have >> s) & 1u) && ld_volatile(arr + s * kMaxOneShotCtas) == tag) have |= 1u << s;
-      if (have == all || __popc(have) >= p.a.req_reduce && p.a.req_reduce < P) break;
-      if (give_up(c, spins, c.deadline)) break;
+      have |= __ballot_sync(0xffffffffu, lane < P && ld_volatile(arr + lane * kMaxOneShotCtas) == tag);
+      if (have == all_ranks || (__popc(have) >= p.a.req_reduce && p.a.req_reduce < P)) break;
+      if ((++spins & (kSlowPoll - 1)) == 0) {
+        const uint32_t gone = peers_gone(p, c) & ~have;  // dead, or told us they left us out: nothing more to come
+        if (gone != 0 && __popc(have | gone) >= P) {
+          have |= __ballot_sync(0xffffffffu, lane < P && ld_volatile(arr + lane * kMaxOneShotCtas) == tag);
+          break;
+        }
+        if (__shfl_sync(0xffffffffu, (lane == 0 && give_up_now(c, c.deadline)) ? 1 : 0, 0) != 0) break;
+      }
     }
-    __threadfence();
-    sh_mask = have;
+    if (lane < P && ((have >> lane) & 1u)) (void)ld_acquire_sys(arr + lane * kMaxOneShotCtas);  // acquire: the senders' data
+    __syncwarp();
+    if (lane == 0) sh_mask = have;
   }
   __syncthreads();
   const uint32_t mask = sh_mask;
@@ -952,7 +746,6 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
     using UW = Unit<TW, E>;
     using UO = Unit<TIn, E>;
     int done = 0;
-    const uint32_t all_ranks = (1u << P) - 1u;
     if (kPull && vec && sizeof(typename UW::raw_t) == 16 && p.a.mc_base != nullptr && p.a.oneshot_pull == 1 &&
         mask == all_ranks) {
       // in-switch reduction of the P staged copies: one request per 16 bytes, eight in flight per thread
@@ -1032,10 +825,13 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
     uint32_t* fin = reinterpret_cast<uint32_t*>(scratch + p.scr.off_fin_cnt);
     __threadfence();
     if (atomicAdd(fin, 1u) == static_cast<uint32_t>(nct - 1)) {
+      const uint32_t dead = ld_volatile(fin + 4);
       st_volatile(fin, 0u);
+      st_volatile(fin + 1, 0u);  // the destination mask of this launch
       __threadfence();
       for (int i = 0; i < P; ++i) {
         const int q = (i + rank) % P;
+        if ((dead >> q) & 1u) continue;
         st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[q] + p.sym.off_done) + rank, tag);
       }
       if (c.host != nullptr) c.host[1] = tag;
@@ -1045,36 +841,74 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
 
 // ---------------------------------------------------------------- host side
 constexpr int kMaxDevices = 64;
+static int wire_bytes_of(int dtype) { return dtype == AAR_BF16 ? 2 : 4; }
 thread_local std::string g_error;
 int fail(int code, const std::string& what) {
   g_error = what;
   return code;
 }
 
-template <typename TIn, typename TW, bool kNvls>
-int launch_twoshot(const KParams& kp, cudaStream_t stream) {
-  auto* fn = aar_twoshot_kernel<TIn, TW, kNvls>;
-  // The shared-memory opt-in is a per-device attribute of the function: once per (instantiation, device).
-  static std::atomic<bool> configured[kMaxDevices];
+// CTAs of `fn` that can be resident at once on the current device (the kernels spin on their peers'
+// flags and on their own control CTA: a CTA that is not resident would never be waited out).
+template <typename F>
+int resident_ctas(F* fn, int smem, int* out) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, int> cache;  // (kernel, device) -> resident CTAs
   int dev = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return fail(AAR_ECUDA, "cudaGetDevice failed");
-  if (dev >= kMaxDevices || !configured[dev].load(std::memory_order_acquire)) {
-    cudaError_t ea = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-    if (ea != cudaSuccess) return fail(AAR_ECUDA, std::string("cudaFuncSetAttribute(smem): ") + cudaGetErrorString(ea));
-    if (dev < kMaxDevices) configured[dev].store(true, std::memory_order_release);
+  std::lock_guard<std::mutex> lock(mu);
+  const auto key = std::make_pair(reinterpret_cast<const void*>(fn), dev);
+  auto it = cache.find(key);
+  if (it == cache.end()) {
+    int sms = 0, per_sm = 0;
+    if (smem > 0) {  // the shared-memory opt-in is a per-device attribute of the function
+      cudaError_t ea = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (ea != cudaSuccess) return fail(AAR_ECUDA, std::string("cudaFuncSetAttribute(smem): ") + cudaGetErrorString(ea));
+    }
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kThreads, smem) != cudaSuccess)
+      return fail(AAR_ECUDA, "occupancy query failed");
+    it = cache.emplace(key, sms * (per_sm > 0 ? per_sm : 1)).first;
   }
-  const int smem = kp.a.use_tma ? kSmemBytes : 0;
-  dim3 grid(kp.a.ctas + 1, kp.a.emu ? kp.a.world : 1);
+  *out = it->second;
+  return 0;
+}
+
+template <typename F>
+int launch_round(F* fn, const KParams& kp_in, int smem, cudaStream_t stream, const char* what) {
+  int resident = 0;
+  if (int rc = resident_ctas(fn, smem, &resident)) return rc;
+  const int ranks_here = kp_in.a.emu ? kp_in.a.world : 1;
+  // Every CTA of the launch must be resident (they wait on each other and on the peers): `ctas` is clamped
+  // to what this device holds.  The work split only depends on kp.a.ctas, so clamping here is enough.
+  const int most = resident / ranks_here - 1;
+  if (most < 1) return fail(AAR_EINVAL, std::string(what) + ": this device cannot keep a control CTA and a work CTA for " +
+                                            std::to_string(ranks_here) + " ranks resident at once");
+  KParams kp = kp_in;
+  if (kp.a.ctas > most) kp.a.ctas = most;
+  dim3 grid(kp.a.ctas + 1, ranks_here);
   cudaError_t e;
   if (kp.a.emu) {
-    void* args[] = {const_cast<KParams*>(&kp)};
+    void* args[] = {&kp};
     e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(fn), grid, dim3(kThreads), args, smem, stream);
   } else {
     fn<<<grid, kThreads, smem, stream>>>(kp);
     e = cudaGetLastError();
   }
-  if (e != cudaSuccess) return fail(AAR_ECUDA, std::string("two-shot launch: ") + cudaGetErrorString(e));
+  if (e != cudaSuccess) return fail(AAR_ECUDA, std::string(what) + " launch: " + cudaGetErrorString(e));
   return 1;
+}
+
+template <typename TIn, typename TW, bool kNvls>
+int launch_twoshot(const KParams& kp, cudaStream_t stream) {
+  // (the TMA ring is reserved even when this launch never touches it: the occupancy this kernel is
+  // launched against must not depend on the launch)
+  return launch_round(aar_twoshot_kernel<TIn, TW, kNvls>, kp, kSmemBytes, stream, "two-shot");
+}
+
+template <typename TW, bool kNvls>
+int launch_stream(const KParams& kp, cudaStream_t stream) {
+  return launch_round(aar_stream_kernel<TW, kNvls>, kp, 0, stream, "stream");
 }
 
 template <typename TIn, typename TW>
@@ -1098,13 +932,158 @@ int launch_oneshot(const KParams& kp, cudaStream_t stream) {
 }
 
 template <typename TIn, typename TW>
-int launch_algo(const KParams& kp, cudaStream_t stream) {
+int launch_algo(const KParams& kp, cudaStream_t stream, bool stream_kernel) {
   if (kp.a.algo == AAR_ALGO_ONESHOT) return launch_oneshot<TIn, TW>(kp, stream);
+  if constexpr (std::is_same<TIn, TW>::value) {
+    if (stream_kernel)
+      return kp.a.algo == AAR_ALGO_NVLS ? launch_stream<TW, true>(kp, stream) : launch_stream<TW, false>(kp, stream);
+  }
   if (kp.a.algo == AAR_ALGO_NVLS) return launch_twoshot<TIn, TW, true>(kp, stream);
   return launch_twoshot<TIn, TW, false>(kp, stream);
 }
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Everything aar_allreduce_round() derives from a launch description before it picks a kernel.
+int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
+  if (a == nullptr) return fail(AAR_EINVAL, "null launch");
+  if (a->world < 1 || a->world > AAR_MAX_RANKS) return fail(AAR_EINVAL, "world must be 1..16");
+  if (a->n <= 0 || a->max_chunk <= 0 || a->L < 1 || a->ctas < 1) return fail(AAR_EINVAL, "bad size/ring/cta arguments");
+  if (a->tag == 0) return fail(AAR_EINVAL, "tag is round+1 and must be > 0");
+  if (a->slot < 0 || a->slot >= a->L) return fail(AAR_EINVAL, "slot must be round % L, in 0..L-1");
+  if (!a->emu && (a->rank < 0 || a->rank >= a->world)) return fail(AAR_EINVAL, "rank must be in 0..world-1");
+  if (a->os_cap < 0) return fail(AAR_EINVAL, "negative one-shot capacity");
+  if (a->block_step != 0 && a->block_step * a->world < a->n) return fail(AAR_EINVAL, "block_step too small");
+  kp.a = *a;
+  const int wb = wire_bytes_of(a->wire_dtype);
+  kp.sym = SymLayout::make(a->n, a->max_chunk, a->world, a->L, wb, a->os_cap, a->block_step);
+  kp.scr = ScratchLayout::make(a->world, kp.sym.cpb);
+  kp.part = Partition(a->n, a->world, kp.sym.block);
+  kp.total_chunks = total_reduced_chunks(kp.part, a->max_chunk);
+  for (int r = 0; r < kMaxRanks; ++r) kp.nch[r] = r < a->world ? num_chunks(kp.part.size(r), a->max_chunk) : 0;
+  kp.zc_src = kp.zc_out = kp.spec_counts = 0;
+  kp.lag_r = kp.lag_c = 0;
+  kp.n_s = kp.n_r = kp.n_c = 0;
+  const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
+  // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
+  const int64_t align_elems = 16 / (in_bytes < wb ? in_bytes : wb);
+  bool vec = (kp.sym.block % align_elems == 0) && (a->max_chunk % align_elems == 0 || a->max_chunk >= kp.sym.block);
+  const int ranks_here = a->emu ? a->world : 1;
+  for (int r = 0; r < ranks_here; ++r) {
+    if (a->src[r] == nullptr || a->out[r] == nullptr || a->scratch[r] == nullptr)
+      return fail(AAR_EINVAL, "src/out/scratch pointer missing");
+    vec = vec && aligned16(a->src[r]) && aligned16(a->out[r]) && (a->counts[r] == nullptr || aligned16(a->counts[r]));
+  }
+  for (int r = 0; r < a->world; ++r)
+    if (a->sym[r] == nullptr) return fail(AAR_EINVAL, "symmetric base pointer missing");
+  kp.vec_ok = vec ? 1 : 0;
+
+  if (a->algo == AAR_ALGO_NVLS) {
+    if (a->mc_base == nullptr || a->emu) return fail(AAR_EUNSUPPORTED, "NVLS needs a multicast alias of the symmetric region");
+    if (a->req_reduce < a->world) return fail(AAR_EINVAL, "NVLS reduces in the switch over all ranks: thReduce must be 1");
+  } else if (a->algo == AAR_ALGO_ONESHOT) {
+    if (a->n > a->os_cap) return fail(AAR_ETOOBIG, "message larger than the one-shot capacity of the region");
+    if (a->L < 2 && a->gate_count <= 0)
+      return fail(AAR_EINVAL, "one-shot needs maxLag >= 1 or the thAllreduce gate (a peer could overwrite a slot in use)");
+    // every rank sums the copies it holds on its own: only with all contributions required do the ranks agree
+    if (a->req_reduce < a->world || a->req_complete < kp.total_chunks)
+      return fail(AAR_EINVAL, "one-shot needs thReduce = thComplete = 1 (ranks reduce independently)");
+  } else if (a->algo != AAR_ALGO_TWOSHOT) {
+    return fail(AAR_EUNSUPPORTED, "unknown algorithm");
+  }
+  if (a->kernel < 0 || a->kernel > 2) return fail(AAR_EINVAL, "kernel must be 0 (auto), 1 (generic) or 2 (stream)");
+  const bool stream_ok = vec && a->in_dtype == a->wire_dtype && a->algo != AAR_ALGO_ONESHOT;
+  if (a->kernel == 2 && !stream_ok)
+    return fail(AAR_EINVAL, "the stream kernel needs 16-byte aligned pointers, block step and chunk size, and src dtype == wire dtype");
+  use_stream = stream_ok && a->kernel != 1;
+
+  // Zero-copy: the caller's tensors ARE this round's staging / sink slots (real ranks only).
+  if (!a->emu && a->algo != AAR_ALGO_ONESHOT && in_bytes == wb) {
+    const uint8_t* src = static_cast<const uint8_t*>(a->src[0]);
+    const uint8_t* out = static_cast<const uint8_t*>(a->out[0]);
+    bool zs = a->scale == 1.0f, zo = true;
+    for (int d = 0; d < a->world; ++d) {
+      if (kp.part.size(d) == 0) continue;
+      const uint8_t* stage = a->algo == AAR_ALGO_NVLS
+                                 ? a->sym[a->rank] + kp.sym.off_scat + kp.sym.scat_elem(a->slot, d) * wb
+                                 : a->sym[d] + kp.sym.off_scat + kp.sym.scat_elem(a->slot, a->rank) * wb;
+      zs = zs && stage == src + kp.part.start(d) * wb;
+      zo = zo && a->sym[a->rank] + kp.sym.off_sink + kp.sym.sink_elem(a->slot, d) * wb == out + kp.part.start(d) * wb;
+    }
+    kp.zc_src = zs ? 1 : 0;
+    kp.zc_out = zo ? 1 : 0;
+  }
+
+  if (a->algo != AAR_ALGO_ONESHOT) {
+    // Every CTA of the launch must be resident (they wait on each other and on the peers): `ctas` is clamped
+    // to what this device holds, before the work is split.
+    int resident = 0;
+    const int rc = use_stream ? resident_ctas(aar_stream_kernel<float, false>, 0, &resident)
+                              : resident_ctas(aar_twoshot_kernel<float, float, false>, kSmemBytes, &resident);
+    if (rc != 0) return rc;
+    const int most = resident / ranks_here - 1;
+    if (most < 1) return fail(AAR_EINVAL, "this device cannot keep a control CTA and a work CTA per rank resident at once");
+    if (kp.a.ctas > most) kp.a.ctas = most;
+  }
+  const int64_t chunk_len = a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1);
+  if (chunk_len >= (int64_t{1} << 31)) return fail(AAR_ETOOBIG, "chunks of 2^31 elements or more: use a smaller maxChunkSize");
+  if (use_stream) {
+    // Warp tiles: about two items per warp and phase, between 4 and 64 warp sweeps (2-32 KB) each; flags stay
+    // per chunk, a self-resetting counter tells the publisher when the last tile of a chunk is in.
+    const int64_t sweep = 32 * (16 / wb);
+    const int64_t warps = static_cast<int64_t>(kp.a.ctas) * kWarps;
+    const int64_t cap = a->part_kb > 0 ? (static_cast<int64_t>(a->part_kb) << 10) / wb : 64 * sweep;
+    auto tile_of = [&](int64_t phase_elems, int& part, int& tpc) {
+      int64_t t = ceil_div(ceil_div(phase_elems, 2 * warps), sweep) * sweep;
+      if (t < 4 * sweep) t = 4 * sweep;
+      if (t > cap) t = ceil_div(cap, sweep) * sweep;
+      const int64_t whole = ceil_div(chunk_len, sweep) * sweep;
+      if (t > whole) t = whole;
+      part = static_cast<int>(t);
+      tpc = static_cast<int>(ceil_div(chunk_len, t));
+    };
+    tile_of(a->n, kp.part_s, kp.tpc_s);
+    tile_of(kp.sym.block, kp.part_r, kp.tpc_r);
+    tile_of(a->n, kp.part_c, kp.tpc_c);
+    kp.lag_r = 1;
+    kp.lag_c = 2;
+    kp.spec_counts = (kp.zc_out && a->counts[0] != nullptr && a->req_reduce >= a->world &&
+                      a->req_complete >= kp.total_chunks) ? 1 : 0;
+    return 0;
+  }
+  const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);
+  const int64_t sweep = static_cast<int64_t>(kThreads) * kUnitsPerThread * unit_elems;
+  // Optional role split (see work_cta).
+  // (Measured on 2 and 8 B200s: one CTA keeps at most ~160 KB in flight, so a phase needs most of the
+  // SMs to reach HBM or NVLink speed and splitting the grid three ways loses more than the overlap
+  // gains.  The split therefore only happens on request: role_s / role_c > 0.)
+  if (a->role_s > 0 && a->role_c > 0 && a->role_s + a->role_c < kp.a.ctas && a->algo != AAR_ALGO_ONESHOT) {
+    kp.n_s = a->role_s;
+    kp.n_c = a->role_c;
+    kp.n_r = kp.a.ctas - kp.n_s - kp.n_c;
+  }
+  // Work items: a chunk is cut into equal parts (multiples of one full CTA sweep) so that each phase has at
+  // least two items per CTA, and no part is larger than `part_kb` (default 256 KB): all CTAs of a phase then
+  // walk through memory inside a window of ctas x part, which keeps the pages they touch at any one time
+  // within TLB reach even for GB-sized messages; flags stay per chunk, a self-resetting counter tells the last
+  // part to raise it.
+  const int64_t cap_elems = (static_cast<int64_t>(a->part_kb > 0 ? a->part_kb : 256) << 10) / wb;
+  auto split = [&](int64_t items_without_split, int ctas_of_role, int& part, int& tpc) {
+    int64_t want = ceil_div(2 * static_cast<int64_t>(ctas_of_role), items_without_split > 0 ? items_without_split : 1);
+    const int64_t for_cap = ceil_div(chunk_len, cap_elems > sweep ? cap_elems : sweep);
+    if (want < for_cap) want = for_cap;
+    const int64_t most = ceil_div(chunk_len, sweep);
+    if (want > most) want = most;
+    if (want < 1) want = 1;
+    int64_t len = ceil_div(ceil_div(chunk_len, want), sweep) * sweep;
+    part = static_cast<int>(len);
+    tpc = static_cast<int>(ceil_div(chunk_len, len));
+  };
+  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.n_s > 0 ? kp.n_s : kp.a.ctas, kp.part_s, kp.tpc_s);
+  split(kp.sym.cpb, kp.n_r > 0 ? kp.n_r : kp.a.ctas, kp.part_r, kp.tpc_r);
+  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.n_c > 0 ? kp.n_c : kp.a.ctas, kp.part_c, kp.tpc_c);
+  return 0;
+}
 
 }  // namespace aar
 
@@ -1113,8 +1092,6 @@ using namespace aar;
 extern "C" {
 
 const char* aar_last_error(void) { return g_error.c_str(); }
-
-static int wire_bytes_of(int dtype) { return dtype == AAR_BF16 ? 2 : 4; }
 
 int64_t aar_sym_bytes(int64_t n, int64_t max_chunk, int world, int L, int wire_dtype, int64_t os_cap,
                       int64_t block_step) {
@@ -1142,94 +1119,54 @@ int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_
   return ScratchLayout::make(world, s.cpb).off_fin_cnt + 8;
 }
 
-int aar_abi_sizeof_launch(void) { return static_cast<int>(sizeof(AarLaunch)); }
-
-int aar_max_emu_ctas(int world, int device) {
-  int sms = 0, per_sm = 0;
-  cudaFuncSetAttribute(aar_twoshot_kernel<float, float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes);
-  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return AAR_ECUDA;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, aar_twoshot_kernel<float, float, false>, kThreads, kSmemBytes) != cudaSuccess)
-    return AAR_ECUDA;
-  const int resident = sms * (per_sm > 0 ? per_sm : 1);
-  return resident / world - 1;
+int64_t aar_scratch_dead_offset(int64_t n, int64_t max_chunk, int world, int64_t block_step) {
+  const SymLayout s = SymLayout::make(n, max_chunk, world, 1, 4, 0, block_step);
+  return ScratchLayout::make(world, s.cpb).off_fin_cnt + 16;
 }
 
-int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
-  if (a == nullptr) return fail(AAR_EINVAL, "null launch");
-  if (a->world < 1 || a->world > AAR_MAX_RANKS) return fail(AAR_EINVAL, "world must be 1..16");
-  if (a->n <= 0 || a->max_chunk <= 0 || a->L < 1 || a->ctas < 1) return fail(AAR_EINVAL, "bad size/ring/cta arguments");
-  if (a->tag == 0) return fail(AAR_EINVAL, "tag is round+1 and must be > 0");
-  if (a->block_step != 0 && a->block_step * a->world < a->n) return fail(AAR_EINVAL, "block_step too small");
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
-  KParams kp;
-  kp.a = *a;
-  const int wb = wire_bytes_of(a->wire_dtype);
-  kp.sym = SymLayout::make(a->n, a->max_chunk, a->world, a->L, wb, a->os_cap, a->block_step);
-  kp.scr = ScratchLayout::make(a->world, kp.sym.cpb);
-  kp.part = Partition(a->n, a->world, kp.sym.block);
-  kp.total_chunks = total_reduced_chunks(kp.part, a->max_chunk);
-  const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
-  const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);
-  // Work items: a chunk is cut into equal parts (multiples of one full CTA sweep) so that each phase has
-  // about two items per CTA; flags stay per chunk, a self-resetting counter tells the last part to raise it.
-  const int64_t sweep = static_cast<int64_t>(kThreads) * kUnitsPerThread * unit_elems;
-  const int64_t chunk_len = a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1);
-  // Optional role split (see work_cta).
-  kp.n_s = kp.n_r = kp.n_c = 0;
-  // (Measured on 2 and 8 B200s: one CTA keeps at most ~160 KB in flight, so a phase needs most of the
-  // SMs to reach HBM or NVLink speed and splitting the grid three ways loses more than the overlap
-  // gains.  The split therefore only happens on request: role_s / role_c > 0.)
-  if (a->role_s > 0 && a->role_c > 0 && a->role_s + a->role_c < a->ctas && a->algo != AAR_ALGO_ONESHOT) {
-    kp.n_s = a->role_s;
-    kp.n_c = a->role_c;
-    kp.n_r = a->ctas - kp.n_s - kp.n_c;
-  }
-  // Work items: a chunk is cut into equal parts (multiples of one full CTA sweep) so that each phase has at
-  // least two items per CTA, and no part is larger than `part_kb` (default 256 KB): all CTAs of a phase then
-  // walk through memory inside a window of ctas x part, which keeps the pages they touch at any one time
-  // within TLB reach even for GB-sized messages.
-  const int64_t cap_elems = (static_cast<int64_t>(a->part_kb > 0 ? a->part_kb : 256) << 10) / wb;
-  auto split = [&](int64_t items_without_split, int ctas_of_role, int& part, int& tpc) {
-    int64_t want = ceil_div(2 * static_cast<int64_t>(ctas_of_role), items_without_split > 0 ? items_without_split : 1);
-    const int64_t for_cap = ceil_div(chunk_len, cap_elems > sweep ? cap_elems : sweep);
-    if (want < for_cap) want = for_cap;
-    const int64_t most = ceil_div(chunk_len, sweep);
-    if (want > most) want = most;
-    if (want < 1) want = 1;
-    int64_t len = ceil_div(ceil_div(chunk_len, want), sweep) * sweep;
-    part = static_cast<int>(len);
-    tpc = static_cast<int>(ceil_div(chunk_len, len));
-  };
-  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.n_s > 0 ? kp.n_s : a->ctas, kp.part_s, kp.tpc_s);
-  split(kp.sym.cpb, kp.n_r > 0 ? kp.n_r : a->ctas, kp.part_r, kp.tpc_r);
-  split(static_cast<int64_t>(kp.sym.cpb) * a->world, kp.n_c > 0 ? kp.n_c : a->ctas, kp.part_c, kp.tpc_c);
-  // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
-  const int64_t align_elems = 16 / (in_bytes < wb ? in_bytes : wb);
-  bool vec = (kp.sym.block % align_elems == 0) && (a->max_chunk % align_elems == 0 || a->max_chunk >= kp.sym.block);
-  const int ranks_here = a->emu ? a->world : 1;
-  for (int r = 0; r < ranks_here; ++r) {
-    if (a->src[r] == nullptr || a->out[r] == nullptr || a->scratch[r] == nullptr)
-      return fail(AAR_EINVAL, "src/out/scratch pointer missing");
-    vec = vec && aligned16(a->src[r]) && aligned16(a->out[r]) && (a->counts[r] == nullptr || aligned16(a->counts[r]));
-  }
-  for (int r = 0; r < a->world; ++r)
-    if (a->sym[r] == nullptr) return fail(AAR_EINVAL, "symmetric base pointer missing");
-  kp.vec_ok = vec ? 1 : 0;
+int aar_abi_sizeof_launch(void) { return static_cast<int>(sizeof(AarLaunch)); }
 
-  if (a->algo == AAR_ALGO_NVLS) {
-    if (a->mc_base == nullptr || a->emu) return fail(AAR_EUNSUPPORTED, "NVLS needs a multicast alias of the symmetric region");
-    if (a->req_reduce < a->world) return fail(AAR_EINVAL, "NVLS reduces in the switch over all ranks: thReduce must be 1");
-  } else if (a->algo == AAR_ALGO_ONESHOT) {
-    if (a->n > a->os_cap) return fail(AAR_ETOOBIG, "message larger than the one-shot capacity of the region");
-    if (a->L < 2 && a->gate_count <= 0)
-      return fail(AAR_EINVAL, "one-shot needs maxLag >= 1 or the thAllreduce gate (a peer could overwrite a slot in use)");
-  } else if (a->algo != AAR_ALGO_TWOSHOT) {
-    return fail(AAR_EUNSUPPORTED, "unknown algorithm");
-  }
-  if (a->in_dtype == AAR_F32 && a->wire_dtype == AAR_F32) return launch_algo<float, float>(kp, stream);
-  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_algo<__nv_bfloat16, __nv_bfloat16>(kp, stream);
-  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_F32) return launch_algo<__nv_bfloat16, float>(kp, stream);
+// Work CTAs per rank that fit next to each other (and their control CTA) on `device`: what `ctas` is
+// clamped against.  kernel: 1 = generic (one CTA per SM), 2 = stream (two per SM).
+int aar_max_ctas(int kernel, int world_on_device, int device) {
+  int prev = 0, resident = 0;
+  if (cudaGetDevice(&prev) != cudaSuccess) return fail(AAR_ECUDA, "cudaGetDevice failed");
+  if (device != prev && cudaSetDevice(device) != cudaSuccess) return fail(AAR_ECUDA, "cudaSetDevice failed");
+  int rc = kernel == 2 ? resident_ctas(aar_stream_kernel<float, false>, 0, &resident)
+                       : resident_ctas(aar_twoshot_kernel<float, float, false>, kSmemBytes, &resident);
+  if (device != prev) cudaSetDevice(prev);
+  if (rc != 0) return rc;
+  if (world_on_device < 1) world_on_device = 1;
+  return resident / world_on_device - 1;
+}
+
+int aar_max_emu_ctas(int world, int device) { return aar_max_ctas(1, world, device); }
+
+int aar_allreduce_round(const AarLaunch* a, void* stream_v) {
+  KParams kp;
+  bool use_stream = false;
+  if (int rc = prepare_round(a, kp, use_stream)) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_v);
+  if (a->in_dtype == AAR_F32 && a->wire_dtype == AAR_F32) return launch_algo<float, float>(kp, stream, use_stream);
+  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_BF16) return launch_algo<__nv_bfloat16, __nv_bfloat16>(kp, stream, use_stream);
+  if (a->in_dtype == AAR_BF16 && a->wire_dtype == AAR_F32) return launch_algo<__nv_bfloat16, float>(kp, stream, use_stream);
   return fail(AAR_EUNSUPPORTED, "dtype combination not supported (f32/f32, bf16/bf16, bf16/f32)");
+}
+
+// Work CTAs aar_allreduce_round() would actually launch for this description (after the residency clamp).
+int aar_round_ctas(const AarLaunch* a) {
+  KParams kp;
+  bool use_stream = false;
+  if (int rc = prepare_round(a, kp, use_stream)) return rc;
+  return kp.a.ctas;
+}
+
+// Which kernel aar_allreduce_round() would run for this launch: 1 generic, 2 stream, 3 one-shot; < 0 = error.
+int aar_round_kernel(const AarLaunch* a) {
+  KParams kp;
+  bool use_stream = false;
+  if (int rc = prepare_round(a, kp, use_stream)) return rc;
+  return a->algo == AAR_ALGO_ONESHOT ? 3 : (use_stream ? 2 : 1);
 }
 
 // ---------------------------------------------------------------- entry point that allocates nothing

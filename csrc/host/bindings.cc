@@ -243,7 +243,8 @@ PYBIND11_MODULE(_aar_host, m) {
       .def_readwrite("max_lag", &MasterConfig::max_lag)
       .def_readwrite("data_size", &MasterConfig::data_size)
       .def_readwrite("max_round", &MasterConfig::max_round)
-      .def_readwrite("max_chunk_size", &MasterConfig::max_chunk_size);
+      .def_readwrite("max_chunk_size", &MasterConfig::max_chunk_size)
+      .def_readwrite("announce_removals", &MasterConfig::announce_removals);
 
   py::class_<MasterEngine>(m, "MasterEngine")
       .def("member_up", &MasterEngine::member_up)

@@ -38,8 +38,16 @@ int MasterEngine::member_up(Endpoint worker) {
 }
 
 void MasterEngine::terminated(Endpoint worker) {
-  for (auto it = workers_.begin(); it != workers_.end();)
-    it = (it->second == worker) ? workers_.erase(it) : std::next(it);
+  bool removed = false;
+  for (auto it = workers_.begin(); it != workers_.end();) {
+    if (it->second == worker) {
+      it = workers_.erase(it);
+      removed = true;
+    } else {
+      ++it;
+    }
+  }
+  if (removed && cfg_.announce_removals && round_ != -1 && !finished()) init_workers(round_);
 }
 
 void MasterEngine::handle(const Message& m) {

@@ -22,6 +22,12 @@ struct MasterConfig {
   int64_t data_size = 10;
   int max_round = 100;
   int64_t max_chunk_size = 2;
+  // Extension: when a worker is removed from a RUNNING job, send the survivors a refreshed InitWorkers (they
+  // treat a second InitWorkers as a peer-map refresh, AllreduceWorker.scala:87-89).  The reference leaves the
+  // stale ActorRef in every worker's map and lets the sends turn into dead letters; a GPU worker has no dead
+  // letters — it would push into, and wait on, the memory of a process that is gone — so the CUDA backend
+  // needs to be told.  Off by default: the engine then behaves message for message like the reference.
+  bool announce_removals = false;
 };
 
 class MasterEngine {

@@ -9,6 +9,8 @@
 //   arr   [L][P][cpb] u32     "ScatterBlock arrived" round tags, written by the sender
 //   rflag [L][P][cpb] u64     "ReduceBlock arrived": round tag << 32 | contributor count
 //   done  [P] u32             CompleteAllreduce: rounds each peer has finished (tag = round+1)
+//   notice[P] u32             skip notices: notice[s] = highest tag for which peer s left ME out of its
+//                             scatter and broadcast (back-pressure); lets a wait give up without the clock
 //   os    [L][P][os_cap]      one-shot path (small messages): every peer's WHOLE message
 //   os_arr[L][P][16] u32      one-shot arrival tags, one per (sender, CTA slice)
 //
@@ -34,7 +36,7 @@ struct SymLayout {
   int64_t block_pad;       // block rounded up to kAlignElems
   int cpb;                 // chunks per (full) block
   int64_t os_cap;          // one-shot capacity in elements (0 = none)
-  int64_t off_arr, off_rflag, off_done, off_os_arr, off_scat, off_sink, off_os, total_bytes;
+  int64_t off_arr, off_rflag, off_done, off_notice, off_os_arr, off_scat, off_sink, off_os, total_bytes;
 
   AAR_HD static int64_t up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
@@ -56,7 +58,8 @@ struct SymLayout {
     s.off_rflag = off;
     off = up(off + (int64_t)L * P * s.cpb * 8, 256);
     s.off_done = off;
-    off = up(off + kMaxRanks * 4, 256);
+    s.off_notice = off + kMaxRanks * 4;  // same 256-byte line group: done[16] | notice[16]
+    off = up(off + 2 * kMaxRanks * 4, 256);
     s.off_os_arr = off;
     off = up(off + (int64_t)L * P * kMaxOneShotCtas * 4, 4096);
     s.off_scat = off;
@@ -86,8 +89,10 @@ struct ScratchLayout {
   int64_t off_red_mask;   // u32 [cpb]      decided contributor mask | kDecided
   int64_t off_fin_cnt;    // u32 [0] CTAs that finished; [1] decided set of scatter destinations;
                           //     [2] force tag, written by the HOST (never reset by the kernel);
-                          //     [3] work CTAs that are past phase R
-  int64_t off_complete;   // u32 [1 + words] completion decision + snapshot bitmap of (owner, chunk)
+                          //     [3] work CTAs that are past phase R;
+                          //     [4] bit mask of peers known dead, written by the HOST (never reset by the kernel)
+  int64_t off_complete;   // u32 [0] completion decision, [1] 1 = every chunk arrived with all P contributors,
+                          //     [4 + words] snapshot bitmap of (owner, chunk)
   int64_t total_bytes;
 
   AAR_HD static ScratchLayout make(int P, int cpb) {
@@ -102,7 +107,7 @@ struct ScratchLayout {
     s.off_red_mask = off;
     off += (int64_t)cpb * 4;
     s.off_fin_cnt = off;
-    off += 16;
+    off += 32;
     s.off_complete = off;
     off += 16 + ((int64_t)P * cpb + 31) / 32 * 4;
     s.total_bytes = SymLayout::up(off, 256);

@@ -30,7 +30,7 @@ typedef struct AarLaunch {
   int32_t algo;             /* AAR_ALGO_* */
   int32_t in_dtype;         /* dtype of src and out: AAR_F32 | AAR_BF16 */
   int32_t wire_dtype;       /* dtype of the symmetric slots */
-  int32_t ctas;             /* work CTAs per rank (one control CTA is added) */
+  int32_t ctas;             /* work CTAs per rank (one control CTA is added); clamped to aar_max_ctas() */
   int32_t use_tma;          /* stage tiles with cp.async.bulk when alignment allows */
   int32_t fast_fences;      /* experiments only: gpu-scope instead of system-scope fences before flags */
   int32_t role_s, role_c;   /* work CTAs dedicated to the scatter / complete phases; 0 = pick automatically */
@@ -39,6 +39,10 @@ typedef struct AarLaunch {
   int32_t overlap_flush;    /* 1: flush already-delivered chunks between reduce items (overlaps phases R and C) */
   int32_t oneshot_pull;     /* one-shot only. 0: push copies to every peer; 1: stage locally, peers pull (in-switch
                                multimem.ld_reduce when mc_base is set); 2: stage locally, unicast pulls only */
+  int32_t kernel;           /* two-shot / NVLS: 0 = pick (the stream kernel whenever pointers, block step and chunk
+                               size are 16-byte aligned and src dtype == wire dtype), 1 = generic kernel, 2 = stream kernel */
+  int32_t mc_bcast;         /* two-shot: 1 = broadcast reduced tiles with one multimem.st through mc_base instead of
+                               P unicast stores (whenever no destination is skipped); NVLS always does */
   int64_t n, max_chunk;     /* dataSize, maxChunkSize (elements) */
   int64_t os_cap;           /* one-shot capacity the region was laid out with */
   int64_t block_step;       /* 0 = reference partition ceil(n/world); else an aligned step >= that */
@@ -84,6 +88,11 @@ int64_t aar_scratch_bytes(int64_t n, int64_t max_chunk, int world, int64_t block
  * every wait immediately (device form of the catch-up path, AllreduceWorker.scala:100-106). */
 int64_t aar_scratch_force_offset(int64_t n, int64_t max_chunk, int world, int64_t block_step);
 
+/* Byte offset, inside a rank's scratch, of the u32 bit mask of peers known dead (bit q = rank q).  The host
+ * sets it when the coordinator reports a worker gone (AllreduceMaster.scala:46-52 drops it from the map,
+ * AllreduceWorker.scala:213-216 then skips it): the kernels neither push to nor wait for those ranks. */
+int64_t aar_scratch_dead_offset(int64_t n, int64_t max_chunk, int world, int64_t block_step);
+
 /* sizeof(AarLaunch) as this library was compiled: bindings compare it with their own mirror of the struct. */
 int aar_abi_sizeof_launch(void);
 
@@ -114,8 +123,16 @@ int aar_allreduce_round(const AarLaunch* launch, void* stream);
  *   (different streams, or two engines) would corrupt each other's counters: serialise them. */
 int aar_allreduce_round_static_scratch(const AarLaunch* launch, void* stream);
 
-/* Co-residency limit for emulation mode: max work CTAs per rank so that world*(ctas+1) blocks fit. */
+/* Co-residency limit: the kernels wait on flags written by their own control CTA and by their peers, so
+ * every CTA of a launch must be resident.  Largest `ctas` for which (ctas+1) x world_on_device CTAs fit on
+ * `device`; kernel: 1 = generic (one CTA per SM), 2 = stream (two per SM).  aar_allreduce_round() refuses
+ * launches beyond it.  aar_max_emu_ctas(world, device) = aar_max_ctas(1, world, device). */
+int aar_max_ctas(int kernel, int world_on_device, int device);
 int aar_max_emu_ctas(int world, int device);
+/* Which kernel aar_allreduce_round() would run for this launch: 1 generic, 2 stream, 3 one-shot; < 0 = error. */
+int aar_round_kernel(const AarLaunch* launch);
+/* Work CTAs that launch would really use: launch->ctas clamped to aar_max_ctas() of its kernel. */
+int aar_round_ctas(const AarLaunch* launch);
 
 /* Symmetric heap (csrc/cuda/sym_heap.cu): CUDA VMM allocation shared with every peer process
  * through POSIX file descriptors passed over unix sockets, plus an NVLS multicast alias when

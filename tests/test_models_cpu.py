@@ -51,17 +51,28 @@ def test_numa_placement_helpers(tmp_path, monkeypatch):
     try:
         got = A.bind_to_gpu(0, str(tmp_path))
         if len(allowed) // 2 >= A.MIN_LOCAL_CPUS:
-            assert got == {"numa_node": 1, "cpus": len(allowed) // 2}
+            assert got == {"bound": True, "numa_node": 1, "cpus": len(allowed) // 2, "source": "sysfs"}
             assert os.sched_getaffinity(0) == set(allowed[: len(allowed) // 2])
         else:
-            assert got is None
+            assert got["bound"] is False and "reason" in got
     finally:
         os.sched_setaffinity(0, before)
     monkeypatch.setenv("AAR_NO_AFFINITY", "1")
     assert A.bind_to_gpu(0, str(tmp_path)) is None
     monkeypatch.delenv("AAR_NO_AFFINITY")
     monkeypatch.setattr(A, "pci_address", lambda i: None)
-    assert A.bind_to_gpu(0, str(tmp_path)) is None
+    monkeypatch.setattr(A, "nvml_cpus_of_gpu", lambda i: set())
+    got = A.bind_to_gpu(0, str(tmp_path))   # nothing names the GPU's cores: nothing bound, and the record says why
+    assert got["bound"] is False and "reason" in got
+    # a container that hides sysfs: NVML's CPU affinity for the device is used instead
+    half = set(allowed[: len(allowed) // 2])
+    monkeypatch.setattr(A, "nvml_cpus_of_gpu", lambda i: half)
+    try:
+        got = A.bind_to_gpu(0, str(tmp_path))
+        if len(half) >= A.MIN_LOCAL_CPUS:
+            assert got == {"bound": True, "numa_node": None, "cpus": len(half), "source": "nvml"}
+    finally:
+        os.sched_setaffinity(0, before)
 
 
 def test_bench_roofline_bookkeeping(tmp_path):
