@@ -962,7 +962,7 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   kp.total_chunks = total_reduced_chunks(kp.part, a->max_chunk);
   for (int r = 0; r < kMaxRanks; ++r) kp.nch[r] = r < a->world ? num_chunks(kp.part.size(r), a->max_chunk) : 0;
   kp.zc_src = kp.zc_out = kp.spec_counts = 0;
-  kp.lag_r = kp.lag_c = 0;
+  kp.warps_s = kp.warps_r = 0;
   kp.n_s = kp.n_r = kp.n_c = 0;
   const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
   // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
@@ -1028,12 +1028,23 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   const int64_t chunk_len = a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1);
   if (chunk_len >= (int64_t{1} << 31)) return fail(AAR_ETOOBIG, "chunks of 2^31 elements or more: use a smaller maxChunkSize");
   if (use_stream) {
-    // Warp tiles: about two items per warp and phase, between 4 and 64 warp sweeps (2-32 KB) each; flags stay
-    // per chunk, a self-resetting counter tells the publisher when the last tile of a chunk is in.
+    // Warps of every CTA are split between the three phases by what each has to move.  Scatter and completion are
+    // copies (HBM, or NVLink egress for the push scatter); reduce+broadcast is the NVLink-bound part and gets the
+    // rest.  With a zero-copy source there is nothing to scatter; with a zero-copy sink and all thresholds 1 the
+    // completion phase only streams counts out of a shared tile (one lane per warp issues bulk stores).
+    const bool spec = kp.zc_out && a->counts[0] != nullptr && a->req_reduce >= a->world && a->req_complete >= kp.total_chunks;
+    int ws = kp.zc_src ? 0 : 5, wc = spec ? 1 : (kp.zc_out && a->counts[0] == nullptr ? 1 : 5);
+    if (a->role_s > 0 && !kp.zc_src) ws = a->role_s;   // (experiments: AAR_ROLE_S / AAR_ROLE_C warps per CTA)
+    if (a->role_c > 0) wc = a->role_c;
+    if (ws + wc > kWarps - 2) return fail(AAR_EINVAL, "role_s + role_c leave fewer than 2 of the 16 warps of a CTA for the reduce phase");
+    kp.warps_s = ws;
+    kp.warps_r = kWarps - ws - wc;
+    // Warp tiles: about two items per warp of the phase's role, between 4 and 64 warp sweeps (2-32 KB) each; flags
+    // stay per chunk, a self-resetting counter tells the publisher when the last tile of a chunk is in.
     const int64_t sweep = 32 * (16 / wb);
-    const int64_t warps = static_cast<int64_t>(kp.a.ctas) * kWarps;
     const int64_t cap = a->part_kb > 0 ? (static_cast<int64_t>(a->part_kb) << 10) / wb : 64 * sweep;
-    auto tile_of = [&](int64_t phase_elems, int& part, int& tpc) {
+    auto tile_of = [&](int64_t phase_elems, int role_warps, int& part, int& tpc) {
+      const int64_t warps = static_cast<int64_t>(kp.a.ctas) * (role_warps > 0 ? role_warps : 1);
       int64_t t = ceil_div(ceil_div(phase_elems, 2 * warps), sweep) * sweep;
       if (t < 4 * sweep) t = 4 * sweep;
       if (t > cap) t = ceil_div(cap, sweep) * sweep;
@@ -1042,13 +1053,10 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
       part = static_cast<int>(t);
       tpc = static_cast<int>(ceil_div(chunk_len, t));
     };
-    tile_of(a->n, kp.part_s, kp.tpc_s);
-    tile_of(kp.sym.block, kp.part_r, kp.tpc_r);
-    tile_of(a->n, kp.part_c, kp.tpc_c);
-    kp.lag_r = 1;
-    kp.lag_c = 2;
-    kp.spec_counts = (kp.zc_out && a->counts[0] != nullptr && a->req_reduce >= a->world &&
-                      a->req_complete >= kp.total_chunks) ? 1 : 0;
+    tile_of(a->n, ws, kp.part_s, kp.tpc_s);
+    tile_of(kp.sym.block, kp.warps_r, kp.part_r, kp.tpc_r);
+    tile_of(a->n, wc, kp.part_c, kp.tpc_c);
+    kp.spec_counts = spec ? 1 : 0;
     return 0;
   }
   const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);

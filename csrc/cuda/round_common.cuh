@@ -36,7 +36,7 @@ struct KParams {
   int zc_src;         // the source IS this round's staging slot: phase S moves nothing, only raises flags
   int zc_out;         // the output IS this round's sink slot: phase C writes only the contributor counts
   int spec_counts;    // stream kernel: counts are written as P up front and repaired if a chunk came short
-  int lag_r, lag_c;   // stream kernel: work-list lag (in chunks) of the reduce / complete items behind scatter
+  int warps_s, warps_r;  // stream kernel: warps per CTA that scatter / reduce+broadcast (the rest complete)
 };
 
 struct Ctx {

@@ -33,13 +33,23 @@ def main() -> int:
             failures.append(name)
             print(f"[rank {rank}] FAIL {name}", flush=True)
 
-    # --- thresholds 1, fp32, several shapes, ring wrap, vs fp32 reference and NCCL
-    for n, mc, lag, align, algo in [(1 << 20, 1 << 16, 1, True, "auto"), (1 << 20, 1 << 16, 1, True, "twoshot"),
-                                    (778, 3, 3, False, "auto"), (100003, 4096, 2, False, "auto"),
-                                    (100003, 4096, 2, False, "twoshot"), (1 << 22, 1 << 18, 1, False, "auto"),
-                                    (256, 256, 1, False, "oneshot"), (50000, 4096, 1, False, "auto")]:
-        eng = DeviceAllreduce(rank, world, n, mc, max_lag=lag, th_allreduce=1.0, device=local,
-                              uds_dir=default_uds_dir(), align_blocks=align, timeout_ms=20_000, algo=algo)
+    # --- thresholds 1, fp32, several shapes, ring wrap, both two-shot kernels, vs fp32 reference and NCCL
+    shapes = [(1 << 20, 1 << 16, 1, True, "auto", None), (1 << 20, 1 << 16, 1, True, "twoshot", "stream"),
+              (1 << 20, 1 << 16, 1, True, "twoshot", "generic"), (1 << 20, 1 << 16, 1, True, "nvls", "stream"),
+              (1 << 20, 1 << 16, 1, True, "nvls", "generic"), (3 << 20, 1 << 18, 2, True, "nvls", "stream"),
+              (778, 3, 3, False, "auto", None), (100003, 4096, 2, False, "auto", None),
+              (100003, 4096, 2, False, "twoshot", None), (1 << 22, 1 << 18, 1, False, "auto", None),
+              (256, 256, 1, False, "oneshot", None), (50000, 4096, 1, False, "auto", None)]
+    for n, mc, lag, align, algo, kernel in shapes:
+        try:
+            eng = DeviceAllreduce(rank, world, n, mc, max_lag=lag, th_allreduce=1.0, device=local,
+                                  uds_dir=default_uds_dir(), align_blocks=align, timeout_ms=20_000, algo=algo, kernel=kernel)
+        except Exception as e:
+            if algo == "nvls" and "multicast" in str(e):   # no NVLS on this box: every rank lands here together
+                if rank == 0:
+                    print(f"skip nvls n={n}: {e}", flush=True)
+                continue
+            raise
         out = torch.empty(n, device=dev)
         cnt = torch.empty(n, dtype=torch.int32, device=dev)
         for r in range(2 * (lag + 1) + 1):
@@ -53,44 +63,68 @@ def main() -> int:
             dist.all_reduce(nccl)
             torch.cuda.synchronize()
             if eng.algo == "nvls":  # the switch fixes the summation order, not us: compare with a tolerance
-                check(f"sum n={n} r={r}", torch.allclose(out.cpu(), want, rtol=1e-5, atol=1e-5))
+                check(f"sum n={n} r={r} {algo}/{kernel}", torch.allclose(out.cpu(), want, rtol=1e-5, atol=1e-5))
             else:
-                check(f"sum n={n} r={r}", torch.equal(out.cpu(), want))
-            check(f"count n={n} r={r}", bool((cnt == world).all()))
-            check(f"nccl n={n} r={r}", torch.allclose(out, nccl, rtol=1e-5, atol=1e-5))
-        check(f"no timeouts n={n}", eng.timeouts_seen() == 0)
+                check(f"sum n={n} r={r} {algo}/{kernel}", torch.equal(out.cpu(), want))
+            check(f"count n={n} r={r} {algo}/{kernel}", bool((cnt == world).all()))
+            check(f"nccl n={n} r={r} {algo}/{kernel}", torch.allclose(out, nccl, rtol=1e-5, atol=1e-5))
+        check(f"no timeouts n={n} {algo}/{kernel}", eng.timeouts_seen() == 0)
+        # zero-copy views (registered buffers): the producer rewrites the staging slot every round
+        if eng.output_view(0) is not None:
+            L = eng.geo.slots
+            for r in range(2 * L + 1):
+                rr = eng.round
+                all_src = srcs_for(n, torch.float32, 100 + r)
+                iv, ov = eng.input_view(rr), eng.output_view(rr)
+                mine = all_src[rank].to(dev)
+                if iv is not None:
+                    iv.copy_(mine)
+                eng.allreduce(iv if iv is not None else mine, ov, cnt)
+                want = torch.zeros(n)
+                for s in all_src:
+                    want += s
+                torch.cuda.synchronize()
+                check(f"zero-copy sum n={n} r={r} {algo}/{kernel}", torch.allclose(ov.cpu(), want, rtol=1e-5, atol=1e-5))
+                check(f"zero-copy count n={n} r={r} {algo}/{kernel}", bool((cnt == world).all()))
+            check(f"no timeouts (zero-copy) n={n} {algo}/{kernel}", eng.timeouts_seen() == 0)
         if rank == 0:
-            print(f"ok fp32 n={n} mc={mc} lag={lag} multicast={eng.has_multicast} algo={eng.algo}", flush=True)
+            print(f"ok fp32 n={n} mc={mc} lag={lag} multicast={eng.has_multicast} algo={eng.algo} "
+                  f"kernel={'stream' if eng.launcher.stream_expected else 'generic'}", flush=True)
         eng.close()
 
     # --- bf16 wire
     n = 1 << 20
-    eng = DeviceAllreduce(rank, world, n, 1 << 16, dtype=torch.bfloat16, device=local, uds_dir=default_uds_dir(),
-                          timeout_ms=20_000)
-    all_src = srcs_for(n, torch.bfloat16, 5)
-    out = torch.empty(n, dtype=torch.bfloat16, device=dev)
-    eng.allreduce(all_src[rank].to(dev), out, None)
-    torch.cuda.synchronize()
-    want = sum((s.float() for s in all_src[1:]), all_src[0].float())
-    check("bf16", torch.allclose(out.float().cpu(), want, rtol=2 ** -7, atol=1e-2))
-    eng.close()
+    for kernel in ("stream", "generic"):
+        eng = DeviceAllreduce(rank, world, n, 1 << 16, dtype=torch.bfloat16, device=local, uds_dir=default_uds_dir(),
+                              timeout_ms=20_000, kernel=kernel)
+        all_src = srcs_for(n, torch.bfloat16, 5)
+        out = torch.empty(n, dtype=torch.bfloat16, device=dev)
+        eng.allreduce(all_src[rank].to(dev), out, None)
+        torch.cuda.synchronize()
+        want = sum((s.float() for s in all_src[1:]), all_src[0].float())
+        check(f"bf16 {kernel}", torch.allclose(out.float().cpu(), want, rtol=2 ** -7, atol=1e-2))
+        eng.close()
 
     # --- thReduce < 1 with a rank that never scatters (needs >= 3 ranks to be meaningful)
     if world >= 3:
         th = (world - 1) / world
-        eng = DeviceAllreduce(rank, world, n, 1 << 16, th_reduce=th, th_complete=1.0, device=local,
-                              uds_dir=default_uds_dir(), timeout_ms=20_000)
-        out = torch.empty(n, device=dev)
-        cnt = torch.empty(n, dtype=torch.int32, device=dev)
-        all_src = srcs_for(n, torch.float32, 9)
-        eng.allreduce(all_src[rank].to(dev), out, cnt, inj=Injection(mute=1 << (world - 1)))
-        torch.cuda.synchronize()
-        want = torch.zeros(n)
-        for s in all_src[:-1]:
-            want += s
-        check("muted sum", torch.equal(out.cpu(), want))
-        check("muted count", bool((cnt == world - 1).all()))
-        eng.close()
+        for kernel, mcb in (("stream", 0), ("generic", 0), ("stream", 1), ("generic", 1)):
+            os.environ["AAR_MC_BCAST"] = str(mcb)   # 1: ReduceBlock broadcast with one multimem.st (needs NVLS)
+            eng = DeviceAllreduce(rank, world, n, 1 << 16, th_reduce=th, th_complete=1.0, device=local,
+                                  uds_dir=default_uds_dir(), timeout_ms=20_000, kernel=kernel)
+            out = torch.empty(n, device=dev)
+            cnt = torch.empty(n, dtype=torch.int32, device=dev)
+            for r in range(3):
+                all_src = srcs_for(n, torch.float32, 9 + r)
+                eng.allreduce(all_src[rank].to(dev), out, cnt, inj=Injection(mute=1 << (world - 1)))
+                torch.cuda.synchronize()
+                want = torch.zeros(n)
+                for s in all_src[:-1]:
+                    want += s
+                check(f"muted sum {kernel} mc_bcast={mcb} r={r}", torch.equal(out.cpu(), want))
+                check(f"muted count {kernel} mc_bcast={mcb} r={r}", bool((cnt == world - 1).all()))
+            eng.close()
+        os.environ.pop("AAR_MC_BCAST", None)
 
     # --- worker API over the coordinator: AllreduceMaster on rank 0 + one DeviceWorker per rank
     from akka_allreduce_b200 import AllReduceInput, AllreduceConfig

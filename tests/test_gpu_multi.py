@@ -21,3 +21,17 @@ def test_all_visible_gpus():
         f.write(p.stdout + "\n--- stderr ---\n" + p.stderr)
     lines = [l for l in (p.stdout + p.stderr).splitlines() if "FAIL" in l or "Error" in l or "error" in l]
     assert p.returncode == 0, "\n".join(lines[-40:])
+
+
+def test_worker_death_is_absorbed_without_timeouts():
+    """tests/multi_gpu_kill_worker.py: one GPU worker dies mid-job, the coordinator's removal becomes the kernels'
+    dead-peer mask, the survivors finish at full speed with count P-1."""
+    n = min(torch.cuda.device_count(), 8)
+    port = 29950 + os.getpid() % 200
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_kill_worker.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    with open(os.path.join(ROOT, "gpurun_out", "multi_gpu_kill.log"), "w") as f:
+        f.write(p.stdout + "\n--- stderr ---\n" + p.stderr)
+    lines = [l for l in (p.stdout + p.stderr).splitlines() if "FAIL" in l or "Error" in l or "] ok" in l]
+    assert p.returncode == 0, "\n".join(lines[-40:])

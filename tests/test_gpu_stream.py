@@ -24,18 +24,19 @@ def _ref_sum(srcs, ranks=None):
     return acc
 
 
-@pytest.mark.parametrize("world,n,mc,max_lag", [
-    (2, 1 << 20, 1 << 16, 1),
-    (4, 1 << 20, 1 << 15, 2),
-    (8, 1 << 21, 1 << 16, 1),       # 4 chunks per block: the software-pipelined work list
-    (8, 1 << 18, 1 << 18, 1),       # one chunk per block
-    (3, 3 * 4096 + 1024, 1000, 1),  # short last block, chunk size not a multiple of the warp sweep
-    (1, 1 << 20, 1 << 16, 1),       # a single rank: pure HBM traffic
-    (5, 5 * 40960, 8192, 3),
+@pytest.mark.parametrize("world,n,mc,max_lag,align", [
+    (2, 1 << 20, 1 << 16, 1, False),
+    (4, 1 << 20, 1 << 15, 2, False),
+    (8, 1 << 21, 1 << 16, 1, False),      # 4 chunks per block: phases pipelined chunk by chunk
+    (8, 1 << 18, 1 << 18, 1, False),      # one chunk per block
+    (3, 3 * 4096 + 1024, 1000, 1, True),  # short last block, chunk size not a multiple of the warp sweep
+    (1, 1 << 20, 1 << 16, 1, False),      # a single rank: pure HBM traffic
+    (5, 5 * 40960, 8192, 3, False),
+    (6, 100000, 4096, 2, True),           # trailing block much shorter than the others
 ])
-def test_stream_kernel_matches_generic_and_fp32_sum(world, n, mc, max_lag):
-    st = _cluster(world, n, mc, max_lag=max_lag, timeout_ms=5000, kernel="stream")
-    ge = _cluster(world, n, mc, max_lag=max_lag, timeout_ms=5000, kernel="generic")
+def test_stream_kernel_matches_generic_and_fp32_sum(world, n, mc, max_lag, align):
+    st = _cluster(world, n, mc, max_lag=max_lag, timeout_ms=5000, kernel="stream", align_blocks=align)
+    ge = _cluster(world, n, mc, max_lag=max_lag, timeout_ms=5000, kernel="generic", align_blocks=align)
     assert st.kernel_used() == "stream" and ge.kernel_used() == "generic"
     for r in range(2 * (max_lag + 1) + 1):
         srcs = _srcs(world, n, torch.float32, r)
