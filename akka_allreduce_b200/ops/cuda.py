@@ -25,8 +25,8 @@ class AarLaunch(C.Structure):
         ("rank", C.c_int32), ("world", C.c_int32), ("emu", C.c_int32),
         ("algo", C.c_int32), ("in_dtype", C.c_int32), ("wire_dtype", C.c_int32),
         ("ctas", C.c_int32), ("use_tma", C.c_int32), ("fast_fences", C.c_int32),
-        ("role_s", C.c_int32), ("role_c", C.c_int32), ("nvls_unroll", C.c_int32), ("part_kb", C.c_int32), ("overlap_flush", C.c_int32), ("oneshot_pull", C.c_int32),
-        ("kernel", C.c_int32), ("mc_bcast", C.c_int32),
+        ("role_s", C.c_int32), ("role_c", C.c_int32), ("nvls_unroll", C.c_int32), ("part_kb", C.c_int32), ("part_sc_kb", C.c_int32), ("overlap_flush", C.c_int32), ("oneshot_pull", C.c_int32),
+        ("kernel", C.c_int32), ("self_publish", C.c_int32), ("push_chunks", C.c_int32), ("mc_bcast", C.c_int32),
         ("n", C.c_int64), ("max_chunk", C.c_int64), ("os_cap", C.c_int64), ("block_step", C.c_int64),
         ("L", C.c_int32), ("slot", C.c_int32),
         ("tag", C.c_uint32),

@@ -98,6 +98,8 @@ class RoundLauncher:
         a.overlap_flush = int(ov) if ov in ("0", "1") else (1 if g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20) else 0)
         a.oneshot_pull = self.oneshot_pull
         a.kernel, a.mc_bcast = self.kernel, self.mc_bcast
+        a.self_publish = int(os.environ.get("AAR_SELF_PUBLISH", 0))
+        a.push_chunks = int(os.environ.get("AAR_PUSH_CHUNKS", 0))
         a.role_s = int(os.environ.get("AAR_ROLE_S", 0))
         a.role_c = int(os.environ.get("AAR_ROLE_C", 0))
         a.nvls_unroll = int(os.environ.get("AAR_NVLS_UNROLL", 0))
@@ -105,6 +107,7 @@ class RoundLauncher:
         # 2.93 ms, 256 KB 3.01 ms, 1 MB 3.11 ms — smaller windows keep the pages in flight within TLB reach)
         big = g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20)
         a.part_kb = int(os.environ.get("AAR_PART_KB", 64 if (big and not self.stream_expected) else 0))
+        a.part_sc_kb = int(os.environ.get("AAR_PART_SC_KB", 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate

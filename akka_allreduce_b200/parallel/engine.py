@@ -212,7 +212,7 @@ class DeviceAllreduce:
         t = self.trace[1:].cpu().double()  # work CTAs only (row 0 is the control CTA)
         t0 = float(t[:, 0].min())
         us = lambda x: round(float(x) / 1e3, 1)
-        out = {"gate_us": us((t[:, 1] - t0).max()), "end_us": us((t[:, 4] - t0).max())}
+        out = {"gate_us": us((t[:, 1] - t0).max()), "end_us": us((t[:, [4, 10]].max(dim=1).values - t0).max())}
         for role, name, col in ((0, "all", 4), (1, "S", 2), (2, "R", 3), (3, "C", 4), (4, "stream", 4)):
             rows = t[t[:, 8] == role]
             if len(rows) == 0:
@@ -222,12 +222,14 @@ class DeviceAllreduce:
                 entry["wait_us"] = [us(rows[:, 5].min()), us(rows[:, 5].max())]
             if role in (0, 3):
                 entry["wait_c_us"] = [us(rows[:, 6].min()), us(rows[:, 6].max())]
-            if role == 4:
-                entry["wait_us"] = [us(rows[:, 5].min()), us(rows[:, 5].max())]
-                entry["wait_c_us"] = [us(rows[:, 6].min()), us(rows[:, 6].max())]
-                first = rows[:, 2][rows[:, 2] > 0]
-                if len(first):
-                    entry["first_reduce_us"] = [us((first - t0).min()), us((first - t0).max())]
+            if role == 4:  # stream kernel: one time line per warp role (first warp of the role in every CTA)
+                def span(col):
+                    v = rows[:, col][rows[:, col] > 0]
+                    return [us((v - t0).min()), us((v - t0).max())] if len(v) else None
+                entry = {"ctas": len(rows), "S_done_us": span(2), "R_done_us": span(3), "C_done_us": span(4),
+                         "first_reduce_us": span(9), "cta_done_us": span(10),
+                         "wait_r_us": [us(rows[:, 5].min()), us(rows[:, 5].max())],
+                         "wait_c_us": [us(rows[:, 6].min()), us(rows[:, 6].max())]}
             if role == 0:
                 entry["S_done_us"] = [us((rows[:, 2] - t0).min()), us((rows[:, 2] - t0).max())]
                 entry["R_done_us"] = [us((rows[:, 3] - t0).min()), us((rows[:, 3] - t0).max())]

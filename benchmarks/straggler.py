@@ -81,7 +81,8 @@ def distributed(args) -> dict:
         master.start()
     stragglers = set(range(world - args.stragglers, world))      # the last k ranks are slow
     rng = random.Random(rank)
-    state = {"ok": True, "done": 0, "min_count": 99, "zero_elems": 0, "t0": None, "t1": None}
+    state = {"ok": True, "done": 0, "min_count": 99, "zero_elems": 0, "elems": 0, "t0": None, "t1": None, "last": None,
+             "slow_rounds": 0, "hist": {}}
     mine = None
 
     def source(req):
@@ -95,12 +96,20 @@ def distributed(args) -> dict:
     def sink(out):
         if state["t0"] is None:
             state["t0"] = time.perf_counter()
-        state["t1"] = time.perf_counter()
+        now = time.perf_counter()
+        if state["last"] is not None and now - state["last"] > 0.9 * args.timeout_ms * 1e-3:
+            state["slow_rounds"] += 1          # a round that sat out (most of) the in-kernel timeout
+        state["last"] = state["t1"] = now
         state["done"] += 1
         if out.iteration % args.check_every == 0:
             state["ok"] = state["ok"] and check(out.data, out.count)
             state["min_count"] = min(state["min_count"], int(out.count.min()))
             state["zero_elems"] += int((out.count == 0).sum())
+            state["elems"] += out.count.numel()
+            if out.iteration % 16 == 0:       # contributor-count histogram, sampled (it costs a sort)
+                vals, cnts = out.count.unique(return_counts=True)
+                for v, k in zip(vals.tolist(), cnts.tolist()):
+                    state["hist"][v] = state["hist"].get(v, 0) + k
 
     w = DeviceWorker(source, sink, cfg, master_port=cfg.cluster.port, device=local)
     dist.barrier()
@@ -111,8 +120,9 @@ def distributed(args) -> dict:
         master.wait(30)
         master.stop()
     secs = (state["t1"] - state["t0"]) if state["t0"] else float("nan")
-    t = torch.tensor([float(state["ok"]), state["done"], secs, state["min_count"], state["zero_elems"]],
-                     dtype=torch.float64, device=dev)
+    t = torch.tensor([float(state["ok"]), state["done"], secs, state["min_count"], state["zero_elems"], state["elems"],
+                      state["slow_rounds"], float(w.engine.timeouts_seen() if w.engine else -1)]
+                     + [float(state["hist"].get(k, 0)) for k in range(world + 1)], dtype=torch.float64, device=dev)
     allt = [torch.zeros_like(t) for _ in range(world)]
     dist.all_gather(allt, t)
     dist.barrier()
@@ -125,6 +135,12 @@ def distributed(args) -> dict:
             "rounds_per_s_slowest_rank": round(min(r[1] / r[2] for r in rows), 1),
             "partial_sums_match_counts": all(r[0] == 1.0 for r in rows),
             "min_count_seen": int(min(r[3] for r in rows)), "elements_with_count_0": int(sum(r[4] for r in rows)),
+            "elements_checked": int(sum(r[5] for r in rows)),
+            "count_0_share_fast_ranks": round(sum(r[4] for r in fast) / max(1.0, sum(r[5] for r in fast)), 4),
+            "rounds_that_sat_out_a_timeout": {"fast_ranks": int(sum(r[6] for r in fast)), "all_ranks": int(sum(r[6] for r in rows))},
+            "last_round_tag_closed_by_timeout_per_rank": [int(r[7]) for r in rows],
+            "count_histogram_fast_ranks_sampled": {str(k): int(sum(r[8 + k] for r in fast)) for k in range(world + 1)},
+            "checked_every": args.check_every, "timeout_ms": args.timeout_ms, "kernel": os.environ.get("AAR_KERNEL", "auto"),
             "thresholds": "thReduce=thComplete=0.75, thAllreduce=0.75, maxLag=4", "delay_us": args.delay_us,
             "straggle_prob": args.straggle_prob}
 
@@ -139,7 +155,7 @@ if __name__ == "__main__":
     ap.add_argument("--straggle-prob", type=float, default=0.3)
     ap.add_argument("--delay-us", type=int, default=2000)
     ap.add_argument("--timeout-ms", type=float, default=50.0)
-    ap.add_argument("--check-every", type=int, default=5)
+    ap.add_argument("--check-every", type=int, default=1)
     ap.add_argument("--out", default="")
     a = ap.parse_args()
     res = emulated(a) if a.emulate else distributed(a)

@@ -47,6 +47,7 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--no-nccl", action="store_true")
     ap.add_argument("--algo", default="auto")
+    ap.add_argument("--kernel", default=None, help="auto | generic | stream (default: AAR_KERNEL or auto)")
     ap.add_argument("--zero-copy", action="store_true", help="source/sink tensors alias the engine's symmetric slots")
     ap.add_argument("--no-counts", action="store_true")
     ap.add_argument("--trace", action="store_true", help="print per-phase device timestamps of one extra round")
@@ -99,10 +100,11 @@ def main():
                     from akka_allreduce_b200.ops.fused_allreduce import EmulatedCluster
 
                     cl = EmulatedCluster(P, n, mc, max_lag=1, dtype=dtype, ctas=ctas or None, timeout_ms=10_000,
-                                         align_blocks=True)
+                                         align_blocks=True, kernel=args.kernel)
                     srcs = [torch.randn(n, device=dev).to(dtype) for _ in range(P)]
                     ms = timed(lambda i: cl.run_round(srcs), args.iters, args.warmup)
                     used = cl.launcher.ctas
+                    kernel_used = cl.kernel_used()
                     algo_used = "twoshot"
                     zc = False
                     del cl, srcs
@@ -110,7 +112,8 @@ def main():
                     from akka_allreduce_b200.parallel.engine import DeviceAllreduce, default_uds_dir
 
                     eng = DeviceAllreduce(rank, world, n, mc, max_lag=1, dtype=dtype, th_allreduce=1.0, device=local,
-                                          uds_dir=default_uds_dir(), ctas=ctas or None, timeout_ms=10_000, algo=args.algo)
+                                          uds_dir=default_uds_dir(), ctas=ctas or None, timeout_ms=10_000, algo=args.algo,
+                                          kernel=args.kernel)
                     srcs = [torch.randn(n, device=dev).to(dtype) for _ in range(nsrc)]
                     outs = [torch.empty(n, dtype=dtype, device=dev) for _ in range(2)]
                     cnts = [torch.empty(n, dtype=torch.int32, device=dev) for _ in range(2)]
@@ -134,6 +137,7 @@ def main():
                         ms = timed(lambda i: eng.allreduce(srcs[i % nsrc], outs[i % 2], cnts[i % 2]), args.iters, args.warmup)
                     used = eng.launcher.ctas
                     algo_used = eng.algo
+                    kernel_used = "oneshot" if eng.algo == "oneshot" else ("stream" if eng.launcher.stream_expected else "generic")
                     if args.trace:
                         eng.enable_trace()
                         if world > 1:
@@ -146,7 +150,8 @@ def main():
                 row = {"bytes": n * esz, "chunk_bytes": mc * esz, "workers": P, "gpus": world, "ctas": used,
                        "ms": round(ms, 5), "algbw_GBps": round(alg, 2), "busbw_GBps": round(alg * 2 * (P - 1) / P, 2),
                        "emulated": bool(args.emulate), "dtype": args.dtype, "algo": algo_used,
-                       "zero_copy": bool(args.zero_copy) and not args.emulate and zc, "counts": not args.no_counts}
+                       "zero_copy": bool(args.zero_copy) and not args.emulate and zc, "counts": not args.no_counts,
+                       "kernel": kernel_used}
                 if nccl_ms is not None:
                     row["nccl_ms"] = round(nccl_ms, 5)
                     row["nccl_busbw_GBps"] = round(n * esz / (nccl_ms * 1e-3) / 1e9 * 2 * (P - 1) / P, 2)

@@ -963,6 +963,8 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   for (int r = 0; r < kMaxRanks; ++r) kp.nch[r] = r < a->world ? num_chunks(kp.part.size(r), a->max_chunk) : 0;
   kp.zc_src = kp.zc_out = kp.spec_counts = 0;
   kp.warps_s = kp.warps_r = 0;
+  kp.self_publish = 0;
+  kp.nvls_chunks = a->algo == AAR_ALGO_NVLS ? kp.sym.cpb : 0;
   kp.n_s = kp.n_r = kp.n_c = 0;
   const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
   // 16-byte paths need every block start, chunk start and pointer aligned for both dtypes.
@@ -1033,8 +1035,16 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     // rest.  With a zero-copy source there is nothing to scatter; with a zero-copy sink and all thresholds 1 the
     // completion phase only streams counts out of a shared tile (one lane per warp issues bulk stores).
     const bool spec = kp.zc_out && a->counts[0] != nullptr && a->req_reduce >= a->world && a->req_complete >= kp.total_chunks;
-    int ws = kp.zc_src ? 0 : 5, wc = spec ? 1 : (kp.zc_out && a->counts[0] == nullptr ? 1 : 5);
-    if (a->role_s > 0 && !kp.zc_src) ws = a->role_s;   // (experiments: AAR_ROLE_S / AAR_ROLE_C warps per CTA)
+    // Hybrid NVLS: the last `push_chunks` chunks of every block bypass the switch's reduction (unicast push +
+    // local sum), so that the links carry more than the in-switch reduce path can take on its own.
+    // (Not with a zero-copy source: row [q] of the staging slot is the caller's slice for owner q in the NVLS layout
+    // and the landing row of q's pushed slice in the push layout — a pushed chunk would overwrite source data the
+    // peer has yet to read.)
+    if (a->algo == AAR_ALGO_NVLS && a->push_chunks > 0 && !kp.zc_src)
+      kp.nvls_chunks = kp.sym.cpb - a->push_chunks > 0 ? kp.sym.cpb - a->push_chunks : 0;
+    const bool hybrid = a->algo == AAR_ALGO_NVLS && kp.nvls_chunks < kp.sym.cpb;
+    int ws = (kp.zc_src && !hybrid) ? 0 : (kp.zc_src ? 3 : 5), wc = spec ? 1 : (kp.zc_out && a->counts[0] == nullptr ? 1 : 5);
+    if (a->role_s > 0 && ws > 0) ws = a->role_s;   // (experiments: AAR_ROLE_S / AAR_ROLE_C warps per CTA)
     if (a->role_c > 0) wc = a->role_c;
     if (ws + wc > kWarps - 2) return fail(AAR_EINVAL, "role_s + role_c leave fewer than 2 of the 16 warps of a CTA for the reduce phase");
     kp.warps_s = ws;
@@ -1042,8 +1052,13 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     // Warp tiles: about two items per warp of the phase's role, between 4 and 64 warp sweeps (2-32 KB) each; flags
     // stay per chunk, a self-resetting counter tells the publisher when the last tile of a chunk is in.
     const int64_t sweep = 32 * (16 / wb);
-    const int64_t cap = a->part_kb > 0 ? (static_cast<int64_t>(a->part_kb) << 10) / wb : 64 * sweep;
-    auto tile_of = [&](int64_t phase_elems, int role_warps, int& part, int& tpc) {
+    // The copies (scatter, completion) take small tiles: the first ScatterBlock flags of a round can go out only
+    // when the first wave of scatter tiles is through, and the round ends one wave of completion tiles after the
+    // last ReduceBlock flag — the shorter a wave, the shorter the fill and the drain of the pipeline.  Reduce tiles
+    // each start with a flag wait, so they are larger.
+    const int64_t cap_r = a->part_kb > 0 ? (static_cast<int64_t>(a->part_kb) << 10) / wb : 64 * sweep;
+    const int64_t cap_sc = a->part_sc_kb > 0 ? (static_cast<int64_t>(a->part_sc_kb) << 10) / wb : 16 * sweep;
+    auto tile_of = [&](int64_t phase_elems, int role_warps, int64_t cap, int& part, int& tpc) {
       const int64_t warps = static_cast<int64_t>(kp.a.ctas) * (role_warps > 0 ? role_warps : 1);
       int64_t t = ceil_div(ceil_div(phase_elems, 2 * warps), sweep) * sweep;
       if (t < 4 * sweep) t = 4 * sweep;
@@ -1053,10 +1068,14 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
       part = static_cast<int>(t);
       tpc = static_cast<int>(ceil_div(chunk_len, t));
     };
-    tile_of(a->n, ws, kp.part_s, kp.tpc_s);
-    tile_of(kp.sym.block, kp.warps_r, kp.part_r, kp.tpc_r);
-    tile_of(a->n, wc, kp.part_c, kp.tpc_c);
+    tile_of(a->n, ws, cap_sc, kp.part_s, kp.tpc_s);
+    tile_of(kp.sym.block, kp.warps_r, cap_r, kp.part_r, kp.tpc_r);
+    tile_of(a->n, wc, cap_sc, kp.part_c, kp.tpc_c);
     kp.spec_counts = spec ? 1 : 0;
+    // who raises the flags: see AarLaunch.self_publish.  Measured on 2 GPUs (push, 64 MB): publisher 0.134 ms,
+    // data warps 0.156 ms — a system-scope fence per chunk in the middle of the stream costs more than the
+    // publisher's scan latency saves; NVLS stages locally (gpu-scope fences), where the data warps win.
+    kp.self_publish = a->self_publish == 2 ? 1 : (a->self_publish == 1 ? 0 : (a->algo == AAR_ALGO_NVLS ? 1 : 0));
     return 0;
   }
   const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);

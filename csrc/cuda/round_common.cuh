@@ -36,6 +36,8 @@ struct KParams {
   int zc_src;         // the source IS this round's staging slot: phase S moves nothing, only raises flags
   int zc_out;         // the output IS this round's sink slot: phase C writes only the contributor counts
   int spec_counts;    // stream kernel: counts are written as P up front and repaired if a chunk came short
+  int nvls_chunks;    // NVLS: leading chunks of every block that go through the switch; the rest take the unicast push path
+  int self_publish;   // stream kernel: data warps raise their own flags, the publisher warp only sends the zero-copy ones
   int warps_s, warps_r;  // stream kernel: warps per CTA that scatter / reduce+broadcast (the rest complete)
 };
 
@@ -222,19 +224,23 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
     if (!muted) {
       __threadfence();
       if (mc != nullptr && p.a.algo == AAR_ALGO_NVLS && dest_ok == all && skip == 0) {
-        for (int ch = lane; ch < cpb; ch += 32)
+        for (int ch = lane; ch < p.nvls_chunks; ch += 32)
           multimem_st_u32(reinterpret_cast<uint32_t*>(mc + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
       } else {
         for (int e = lane; e < s_entries; e += 32) {
           const int d = e / cpb, ch = e % cpb;
           if (((skip >> d) & 1u) || !((dest_ok >> d) & 1u)) continue;
-          if (ch >= p.nch[d]) continue;
+          if (ch >= p.nch[d] || ch >= p.nvls_chunks) continue;  // (push chunks are flagged by whoever scatters them)
           st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
         }
       }
     }
   }
 
+  if (p.self_publish) {  // nothing to scan: the data warps raise the flags of what they finish
+    if (lane == 0) finish_cta(p, c);
+    return;
+  }
   bool last_pass = false;
   for (;;) {
     const bool closing = ld_volatile(fin + 3) >= static_cast<uint32_t>(p.a.ctas);  // read BEFORE the scan
@@ -245,8 +251,8 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
         const int e = base0 + 32 * w + lane;
         bool ready = false;
         if (e < s_entries) {  // ScatterBlock (d, ch): all parts out?
-          if (!p.zc_src) {
-            const int d = e / cpb, ch = e % cpb;
+          const int d = e / cpb, ch = e % cpb;
+          if (!p.zc_src || ch >= p.nvls_chunks) {
             const int64_t bs = p.part.size(d);
             if (ch < p.nch[d]) {
               const uint32_t want = parts_of(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s);
@@ -270,7 +276,10 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
       bool remote = false;
 #pragma unroll
       for (int w = 0; w < kPubWords; ++w)
-        if ((mine >> w) & 1u) remote = remote || !(p.a.algo == AAR_ALGO_NVLS && base0 + 32 * w + lane < s_entries);
+        if ((mine >> w) & 1u) {
+          const int e = base0 + 32 * w + lane;
+          remote = remote || !(e < s_entries && e % cpb < p.nvls_chunks);  // (nvls_chunks is 0 without NVLS)
+        }
       if (__any_sync(0xffffffffu, remote) && !p.a.fast_fences) __threadfence_system();
       else __threadfence();
 #pragma unroll

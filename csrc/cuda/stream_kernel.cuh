@@ -19,6 +19,9 @@
 //   * with a multicast alias the reduce is one multimem.ld_reduce + one multimem.st per 16 bytes, eight
 //     in flight per lane (NVLS); without it — or for chunks that close short of all P contributors —
 //     the same tile is summed from unicast loads in peer order 0..P-1;
+//   * per-chunk flags are raised either by the publisher warp of the control CTA (it scans the part counters and
+//     pays one fence per batch) or by the data warp that completes the last tile of a chunk (no scan latency, one
+//     fence per chunk; AarLaunch.self_publish);
 //   * per-element contributor counts are pure fill traffic: one elected lane streams them out of an 8 KB
 //     shared tile with cp.async.bulk (TMA) while the other lanes move data.  When the output is the sink
 //     slot itself and every threshold is 1 they are written up front as P and repaired after the
@@ -52,7 +55,7 @@ __device__ __forceinline__ uint4 scale_unit(const uint4& r, float scale) {
 template <typename TW>
 __device__ __forceinline__ void warp_copy_tile(const uint4* __restrict__ s, uint4* __restrict__ d, int units,
                                                float scale, int lane) {
-  constexpr int U = 4;
+  constexpr int U = 8;
   int u0 = lane;
   for (; u0 + 32 * (U - 1) < units; u0 += 32 * U) {  // full sweeps: U loads in flight, no predicates
     uint4 r[U];
@@ -183,7 +186,7 @@ __device__ __forceinline__ bool warp_fill_counts(int32_t* __restrict__ counts, i
 template <typename TW>
 __device__ __forceinline__ void warp_flush_tile(const uint4* __restrict__ sink, uint4* __restrict__ out, int units,
                                                 bool present, int lane) {
-  constexpr int U = 4;
+  constexpr int U = 8;
   if (!present) {
     const uint4 z = make_uint4(0u, 0u, 0u, 0u);
     for (int u = lane; u < units; u += 32) out[u] = z;
@@ -302,16 +305,33 @@ __device__ __noinline__ void scatter_item(const KParams& p, const Ctx& c, const 
   const int64_t off = cb + static_cast<int64_t>(t) * p.part_s;
   if (off >= ce) return;
   if (w.muted || ((w.skip >> d) & 1u) || !((w.dest_ok >> d) & 1u)) return;
+  // NVLS stages the slice in MY scat row [d] for the switch to pull; the trailing `push` chunks of a hybrid round
+  // (and every chunk without NVLS) go straight into owner d's scat row [me] over NVLink.
+  const bool push_ch = !kNvls || ch >= p.nvls_chunks;
+  if (p.zc_src && !push_ch) return;  // staged by the caller before the launch, flagged by the publisher warp
   const int len = static_cast<int>(min(static_cast<int64_t>(p.part_s), ce - off));
-  TW* dst = kNvls ? reinterpret_cast<TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, d) + off
-                  : reinterpret_cast<TW*>(p.a.sym[d] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off;
+  TW* dst = !push_ch ? reinterpret_cast<TW*>(c.my_sym + p.sym.off_scat) + p.sym.scat_elem(c.slot, d) + off
+                     : reinterpret_cast<TW*>(p.a.sym[d] + p.sym.off_scat) + p.sym.scat_elem(c.slot, c.rank) + off;
   const TW* from = static_cast<const TW*>(p.a.src[c.vr]) + p.part.start(d) + off;
   if (reinterpret_cast<const void*>(from) != reinterpret_cast<const void*>(dst))
     warp_copy_tile<TW>(reinterpret_cast<const uint4*>(from), reinterpret_cast<uint4*>(dst), len / E, p.a.scale, w.lane);
   __syncwarp();
-  if (w.lane == 0) {  // the publisher warp raises the ScatterBlock flag once all parts of the chunk are out
+  if (w.lane == 0) {
+    // Part done.  Whoever brings the count to the number of parts of the chunk raises its ScatterBlock flag —
+    // no publisher warp to wait for.  Ordering: every part's stores precede (fence) its increment; the last
+    // incrementer has observed all of them and fences again before the flag, at system scope when the slice went
+    // to a peer over NVLink (a gpu-scope fence is enough for a slice staged locally: the peers read it through
+    // this GPU's L2).  That fence stalls one warp out of thousands, not a CTA.
     __threadfence();
-    atomicAdd(reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt) + d * p.sym.cpb + ch, 1u);
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt) + d * p.sym.cpb + ch;
+    if (!p.self_publish) {
+      atomicAdd(cnt, 1u);  // the publisher warp of the control CTA watches the count
+    } else if (atomicAdd(cnt, 1u) + 1u == parts_of(ce - cb, p.part_s)) {
+      st_volatile(cnt, 0u);
+      if (!push_ch || p.a.fast_fences) __threadfence();
+      else __threadfence_system();
+      st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
+    }
   }
 }
 
@@ -333,24 +353,47 @@ __device__ __noinline__ void reduce_item(const KParams& p, const Ctx& c, const W
     if (*w.first_r == 0) *w.first_r = w1;
   }
   const uint32_t all = all_ranks_mask(c.P);
-  const int cnt = __popc(mask);
+  const int cnt_mask_popc = __popc(mask);
+  const int cnt = cnt_mask_popc;
   const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
   const int64_t sink_off = p.sym.off_sink + (p.sym.sink_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
-  uint4* mc_dst = (w.mc != nullptr && w.dest_ok == all && (kNvls || p.a.mc_bcast)) ? reinterpret_cast<uint4*>(w.mc + sink_off) : nullptr;
-  if (kNvls && mask == all && mc_dst != nullptr) {
+  const bool push_ch = !kNvls || ch >= p.nvls_chunks;
+  uint4* mc_dst = (w.mc != nullptr && w.dest_ok == all && (!push_ch || p.a.mc_bcast)) ? reinterpret_cast<uint4*>(w.mc + sink_off) : nullptr;
+  if (!push_ch && mask == all && mc_dst != nullptr) {
     const int64_t so = p.sym.off_scat + (p.sym.scat_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
     warp_nvls_tile<TW>(reinterpret_cast<const uint4*>(w.mc + so), mc_dst, len / E, post, w.lane);
-  } else if (c.P == 1) {
-    warp_reduce_units<TW, 4, kNvls>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
-  } else if (c.P == 2) {
-    warp_reduce_units<TW, 2, kNvls>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
-  } else {
-    warp_reduce_units<TW, 1, kNvls>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
+  } else if (push_ch) {  // contributions were pushed into my own scat rows
+    if (c.P == 1) warp_reduce_units<TW, 4, false>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
+    else if (c.P == 2) warp_reduce_units<TW, 2, false>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
+    else warp_reduce_units<TW, 1, false>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
+  } else {  // NVLS chunk that closed short of all P contributors: unicast pulls from the peers' staging slots
+    warp_reduce_units<TW, 1, true>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
   }
   __syncwarp();
   if (w.lane == 0) {
+    // Part done; the last part of the chunk raises the ReduceBlock flag (tag | contributor count) on every
+    // destination, behind a system-scope fence: the reduced data went out over NVLink.
     __threadfence();
-    atomicAdd(reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt) + ch, 1u);
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt) + ch;
+    if (!p.self_publish) {
+      atomicAdd(cnt, 1u);
+    } else if (atomicAdd(cnt, 1u) + 1u == parts_of(ce - cb, p.part_r)) {
+      uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask) + ch;
+      st_volatile(cnt, 0u);
+      st_volatile(red_mask, 0u);
+      if (p.a.fast_fences) __threadfence();
+      else __threadfence_system();
+      const uint64_t f = (static_cast<uint64_t>(c.tag) << 32) | static_cast<uint32_t>(cnt_mask_popc);
+      if (w.mc != nullptr && w.dest_ok == all && !p.a.fast_fences) {
+        multimem_st_u64(reinterpret_cast<uint64_t*>(w.mc + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
+      } else {
+        for (int i = 0; i < c.P; ++i) {
+          const int q = (i + c.rank) % c.P;
+          if ((w.dest_ok >> q) & 1u)
+            st_relaxed_sys(reinterpret_cast<uint64_t*>(p.a.sym[q] + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
+        }
+      }
+    }
   }
 }
 
@@ -397,9 +440,9 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
   uint64_t* trace = p.a.trace != nullptr
                         ? p.a.trace + (static_cast<int64_t>(c.vr) * (p.a.ctas + 1) + blockIdx.x) * 16
                         : nullptr;
-  const bool tracer = trace != nullptr && threadIdx.x == 0;
+  const bool tracer0 = trace != nullptr && threadIdx.x == 0;
   uint64_t wait_r = 0, wait_c = 0, first_r = 0;
-  if (tracer) trace[0] = globaltimer_ns();
+  if (tracer0) trace[0] = globaltimer_ns();
 
   for (int i = threadIdx.x; i < kCntTile / 4; i += kThreads) reinterpret_cast<int4*>(cnt_tile)[i] = make_int4(P, P, P, P);
   fence_proxy_async_smem();
@@ -414,7 +457,7 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
     if (lane == 0) sh_dest_ok = m;
   }
   __syncthreads();
-  if (tracer) trace[1] = globaltimer_ns();
+  if (tracer0) trace[1] = globaltimer_ns();
   WarpEnv w;
   w.dest_ok = sh_dest_ok;
   w.skip = p.a.skip_dest_mask[c.rank];
@@ -424,9 +467,6 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
   w.use_tma = p.a.use_tma != 0;
   w.mc = p.a.emu ? nullptr : p.a.mc_base;
   w.cnt_tile = cnt_tile;
-  w.wait_r = tracer ? &wait_r : nullptr;
-  w.wait_c = tracer ? &wait_c : nullptr;
-  w.first_r = tracer ? &first_r : nullptr;
 
   // Role of this warp, and its position among the warps of that role across the grid (consecutive tiles land
   // on different CTAs, so the grid walks through a chunk together and its flag goes out early).
@@ -435,9 +475,14 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
   const int role_warps = role == 0 ? p.warps_s : (role == 1 ? p.warps_r : kWarps - p.warps_s - p.warps_r);
   const int rw = (warp - (role == 0 ? 0 : (role == 1 ? p.warps_s : p.warps_s + p.warps_r))) * p.a.ctas + cta;
   const int stride = role_warps * p.a.ctas;
+  // tracing: lane 0 of the first warp of each role keeps the time line of its role for this CTA
+  const bool tracer = trace != nullptr && lane == 0 && rw == cta;
+  w.wait_r = tracer ? &wait_r : nullptr;
+  w.wait_c = tracer ? &wait_c : nullptr;
+  w.first_r = tracer ? &first_r : nullptr;
   bool bulk = false;
   if (role == 0) {
-    if (!p.zc_src) {
+    if (!p.zc_src || p.nvls_chunks < cpb) {
       const int per_chunk = P * p.tpc_s, total = per_chunk * cpb;
       for (int it = rw; it < total; it += stride) {
         const int ch = it / per_chunk, rem = it - ch * per_chunk;
@@ -486,17 +531,21 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
     }
   }
   if (bulk && lane == 0) tma_wait_all<0>();  // this lane's count stores have landed
+  if (tracer) {  // [2] scatter role done, [3] reduce role done, [4] complete role done, [5]/[6] ns waited in R / C
+    trace[2 + role] = globaltimer_ns();
+    if (role == 1) {
+      trace[5] = wait_r;
+      trace[9] = first_r;
+    }
+    if (role == 2) trace[6] = wait_c;
+  }
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(fin_words(p, c) + 3, 1u);  // tells the publisher that this CTA will add nothing more to its counters
     if (trace != nullptr) {
-      trace[2] = first_r;
-      trace[3] = globaltimer_ns();
-      trace[4] = trace[3];
-      trace[5] = wait_r;
-      trace[6] = wait_c;
-      trace[8] = 4;  // role 4: a CTA of the stream kernel
+      trace[10] = globaltimer_ns();  // all warps of the CTA done
+      trace[8] = 4;                  // role 4: a CTA of the stream kernel
     }
     finish_cta(p, c);
   }

@@ -33,14 +33,21 @@ typedef struct AarLaunch {
   int32_t ctas;             /* work CTAs per rank (one control CTA is added); clamped to aar_max_ctas() */
   int32_t use_tma;          /* stage tiles with cp.async.bulk when alignment allows */
   int32_t fast_fences;      /* experiments only: gpu-scope instead of system-scope fences before flags */
-  int32_t role_s, role_c;   /* work CTAs dedicated to the scatter / complete phases; 0 = pick automatically */
+  int32_t role_s, role_c;   /* generic kernel: work CTAs dedicated to the scatter / complete phases; stream kernel:
+                               warps (of the 16 per CTA) that scatter / complete; 0 = pick automatically */
   int32_t nvls_unroll;      /* multimem.ld_reduce requests in flight per thread: 0/8 = 8, or 16 */
-  int32_t part_kb;          /* largest work item in KB of wire data; 0 = 256 */
+  int32_t part_kb;          /* largest work item in KB of wire data; 0 = 256 (generic), 32 (stream: reduce tiles) */
+  int32_t part_sc_kb;       /* stream kernel: largest scatter / completion tile in KB; 0 = 8 */
   int32_t overlap_flush;    /* 1: flush already-delivered chunks between reduce items (overlaps phases R and C) */
   int32_t oneshot_pull;     /* one-shot only. 0: push copies to every peer; 1: stage locally, peers pull (in-switch
                                multimem.ld_reduce when mc_base is set); 2: stage locally, unicast pulls only */
   int32_t kernel;           /* two-shot / NVLS: 0 = pick (the stream kernel whenever pointers, block step and chunk
                                size are 16-byte aligned and src dtype == wire dtype), 1 = generic kernel, 2 = stream kernel */
+  int32_t self_publish;     /* stream kernel: who raises the per-chunk flags.  1 = the publisher warp of the control CTA
+                               (scans part counters, one fence per batch), 2 = the data warp that completes a chunk's
+                               last part (no scan latency, one fence per chunk), 0 = pick */
+  int32_t push_chunks;      /* NVLS + stream kernel: the last `push_chunks` chunks of every block take the unicast push
+                               path instead of the in-switch reduction (a hybrid round); 0 = all through the switch */
   int32_t mc_bcast;         /* two-shot: 1 = broadcast reduced tiles with one multimem.st through mc_base instead of
                                P unicast stores (whenever no destination is skipped); NVLS always does */
   int64_t n, max_chunk;     /* dataSize, maxChunkSize (elements) */

@@ -1,5 +1,6 @@
 """Real multi-GPU runs (NVLink peers, one process per GPU) of the fused kernel and the worker API."""
 import os
+import socket
 import subprocess
 import sys
 
@@ -10,9 +11,16 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+def _free_port() -> int:
+    """A rendezvous port nobody is listening on (a fixed one can still be in TIME_WAIT from the previous test)."""
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
 def test_all_visible_gpus():
     n = min(torch.cuda.device_count(), 8)
-    port = 29700 + os.getpid() % 200
+    port = _free_port()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_worker.py")]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
@@ -27,7 +35,7 @@ def test_worker_death_is_absorbed_without_timeouts():
     """tests/multi_gpu_kill_worker.py: one GPU worker dies mid-job, the coordinator's removal becomes the kernels'
     dead-peer mask, the survivors finish at full speed with count P-1."""
     n = min(torch.cuda.device_count(), 8)
-    port = 29950 + os.getpid() % 200
+    port = _free_port()
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.join(ROOT, "tests", "multi_gpu_kill_worker.py")]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
