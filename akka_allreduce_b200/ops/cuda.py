@@ -14,6 +14,7 @@ MAX_RANKS = 16
 F32, BF16 = 0, 1
 ALGO_TWOSHOT, ALGO_ONESHOT, ALGO_NVLS = 0, 1, 2
 ALGO_NAMES = {"twoshot": ALGO_TWOSHOT, "oneshot": ALGO_ONESHOT, "nvls": ALGO_NVLS}
+OP_ALLREDUCE, OP_REDUCE_SCATTER, OP_ALL_GATHER = 0, 1, 2
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_STREAM = 0, 1, 2
 KERNEL_NAMES = {"auto": KERNEL_AUTO, "generic": KERNEL_GENERIC, "stream": KERNEL_STREAM}
 
@@ -23,7 +24,7 @@ class AarLaunch(C.Structure):
 
     _fields_ = [
         ("rank", C.c_int32), ("world", C.c_int32), ("emu", C.c_int32),
-        ("algo", C.c_int32), ("in_dtype", C.c_int32), ("wire_dtype", C.c_int32),
+        ("algo", C.c_int32), ("op", C.c_int32), ("in_dtype", C.c_int32), ("wire_dtype", C.c_int32),
         ("ctas", C.c_int32), ("use_tma", C.c_int32), ("fast_fences", C.c_int32),
         ("role_s", C.c_int32), ("role_c", C.c_int32), ("nvls_unroll", C.c_int32), ("part_kb", C.c_int32), ("part_sc_kb", C.c_int32), ("overlap_flush", C.c_int32), ("oneshot_pull", C.c_int32),
         ("kernel", C.c_int32), ("self_publish", C.c_int32), ("push_chunks", C.c_int32), ("mc_bcast", C.c_int32),

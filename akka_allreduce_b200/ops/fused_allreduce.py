@@ -188,15 +188,17 @@ class EmulatedCluster:
         a.host_flags = self.host_flags.data_ptr()
 
     def run_round(self, srcs, inj: Injection | None = None, outs=None, counts=None, round_: int | None = None,
-                  force: bool = False):
+                  force: bool = False, op: int = K.OP_ALLREDUCE):
         """One allreduce round over ``srcs`` (one tensor per virtual rank). Returns (outs, counts)."""
         r = self.round if round_ is None else round_
         outs = outs or self.outs
         counts = counts or self.counts
         a = self._a
         self.launcher.fill(a, r, inj)
+        a.op = op
         for i in range(self.world):
-            assert srcs[i].numel() == self.geo.n and srcs[i].dtype == self.launcher.dtype and srcs[i].is_contiguous()
+            want = self.geo.size(i) if op == K.OP_ALL_GATHER else self.geo.n
+            assert srcs[i].numel() == want and srcs[i].dtype == self.launcher.dtype and srcs[i].is_contiguous()
             a.src[i] = srcs[i].data_ptr()
             a.out[i] = outs[i].data_ptr()
             a.counts[i] = counts[i].data_ptr()
@@ -204,7 +206,10 @@ class EmulatedCluster:
             off = self.launcher.force_offset
             self.scratch[:, off:off + 4].view(torch.int32).fill_((r + 1) if force else 0)
             self._forced = force
-        self.launcher.launch(a)
+        try:
+            self.launcher.launch(a)
+        finally:
+            a.op = K.OP_ALLREDUCE
         if round_ is None:
             self.round += 1
         return outs, counts

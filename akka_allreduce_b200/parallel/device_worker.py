@@ -184,7 +184,11 @@ class DeviceWorker:
             r = inflight.pop(0)
             slot = r % L
             events[slot].synchronize()
-            self.sink(AllReduceOutput(outs[slot], counts[slot], r))
+            # The sink runs with the round stream current: whatever GPU work it enqueues on the views (a checksum,
+            # an optimizer step) is ordered before the launch that recycles this slot maxLag + 1 rounds later, so a
+            # sink need not synchronise to be safe.
+            with torch.cuda.stream(stream):
+                self.sink(AllReduceOutput(outs[slot], counts[slot], r))
             self._node.report_complete(self.id, r)
             self.round = r + 1
             self.rounds_completed += 1

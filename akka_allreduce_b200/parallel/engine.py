@@ -198,6 +198,51 @@ class DeviceAllreduce:
         if round_ is None:
             self.round += 1
 
+    # ---- the two halves of the round on their own (the scatter->reduce half is a reduce-scatter,
+    # the broadcast half an all-gather; AllreduceWorker.scala:212-238 and :252-268) ---------------------------
+    def block_range(self, rank: int | None = None) -> tuple[int, int]:
+        """Element range of the block ``rank`` (default: this rank) owns."""
+        r = self.rank if rank is None else rank
+        return self.geo.start(r), self.geo.end(r)
+
+    def _half_round(self, op: int, src: torch.Tensor, out: torch.Tensor, counts: torch.Tensor | None,
+                    stream: torch.cuda.Stream | None) -> None:
+        if self.algo == "oneshot" or not self.launcher.stream_expected:
+            raise K.AarError("reduce_scatter / all_gather need the stream kernel: aligned blocks (align_blocks=True), "
+                             "dtype == wire dtype, and a two-shot or NVLS engine (algo != oneshot)")
+        a = self._launch
+        self.launcher.fill(a, self.round, None)
+        a.op = op
+        a.src[0], a.out[0] = src.data_ptr(), out.data_ptr()
+        a.counts[0] = counts.data_ptr() if counts is not None else None
+        try:
+            self.launcher.launch(a, stream)
+        finally:
+            a.op = K.OP_ALLREDUCE
+        self.round += 1
+
+    def reduce_scatter(self, src: torch.Tensor, out_block: torch.Tensor, counts_block: torch.Tensor | None = None,
+                       stream: torch.cuda.Stream | None = None) -> None:
+        """``out_block`` <- this rank's block of the sum of every rank's ``src`` (the whole message);
+        ``counts_block`` <- contributors per element of that block.  Uses one round of the ring."""
+        lo, hi = self.block_range()
+        if src.numel() != self.geo.n or out_block.numel() != hi - lo or (counts_block is not None and counts_block.numel() != hi - lo):
+            raise ValueError(f"reduce_scatter: src must hold {self.geo.n} elements, out_block / counts_block {hi - lo}")
+        if src.dtype != self.launcher.dtype or out_block.dtype != self.launcher.dtype:
+            raise ValueError("dtype differs from the engine's")
+        self._half_round(K.OP_REDUCE_SCATTER, src, out_block, counts_block, stream)
+
+    def all_gather(self, src_block: torch.Tensor, out: torch.Tensor, counts: torch.Tensor | None = None,
+                   stream: torch.cuda.Stream | None = None) -> None:
+        """``out`` <- every rank's ``src_block`` at its owner's block range; ``counts`` <- 1 where a block arrived,
+        0 (and zeros in ``out``) where it did not before the round closed (thComplete / timeout)."""
+        lo, hi = self.block_range()
+        if src_block.numel() != hi - lo or out.numel() != self.geo.n or (counts is not None and counts.numel() != self.geo.n):
+            raise ValueError(f"all_gather: src_block must hold {hi - lo} elements, out / counts {self.geo.n}")
+        if src_block.dtype != self.launcher.dtype or out.dtype != self.launcher.dtype:
+            raise ValueError("dtype differs from the engine's")
+        self._half_round(K.OP_ALL_GATHER, src_block, out, counts, stream)
+
     def enable_trace(self) -> torch.Tensor:
         """Per-CTA phase timestamps of the LAST launch: int64 [ctas+1, 8] of globaltimer ns
         (start, gate passed, S done, R done, C done, ns waiting in R, ns waiting in C, 0)."""

@@ -993,14 +993,23 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   } else if (a->algo != AAR_ALGO_TWOSHOT) {
     return fail(AAR_EUNSUPPORTED, "unknown algorithm");
   }
+  if (a->op < AAR_OP_ALLREDUCE || a->op > AAR_OP_ALL_GATHER) return fail(AAR_EINVAL, "op must be AAR_OP_ALLREDUCE, _REDUCE_SCATTER or _ALL_GATHER");
   if (a->kernel < 0 || a->kernel > 2) return fail(AAR_EINVAL, "kernel must be 0 (auto), 1 (generic) or 2 (stream)");
   const bool stream_ok = vec && a->in_dtype == a->wire_dtype && a->algo != AAR_ALGO_ONESHOT;
   if (a->kernel == 2 && !stream_ok)
     return fail(AAR_EINVAL, "the stream kernel needs 16-byte aligned pointers, block step and chunk size, and src dtype == wire dtype");
   use_stream = stream_ok && a->kernel != 1;
+  if (a->op != AAR_OP_ALLREDUCE) {
+    if (!use_stream) return fail(AAR_EUNSUPPORTED, "reduce-scatter / all-gather rounds run on the stream kernel only (aligned buffers, src dtype == wire dtype, not one-shot)");
+    if (a->op == AAR_OP_REDUCE_SCATTER) {  // the round ends with my own block: its chunks always get reduced
+      kp.total_chunks = kp.nch[a->emu ? 0 : a->rank];
+      kp.a.req_complete = kp.total_chunks;
+      if (a->emu) return fail(AAR_EUNSUPPORTED, "reduce-scatter rounds are not emulated (per-rank completion counts)");
+    }
+  }
 
   // Zero-copy: the caller's tensors ARE this round's staging / sink slots (real ranks only).
-  if (!a->emu && a->algo != AAR_ALGO_ONESHOT && in_bytes == wb) {
+  if (!a->emu && a->algo != AAR_ALGO_ONESHOT && in_bytes == wb && a->op == AAR_OP_ALLREDUCE) {
     const uint8_t* src = static_cast<const uint8_t*>(a->src[0]);
     const uint8_t* out = static_cast<const uint8_t*>(a->out[0]);
     bool zs = a->scale == 1.0f, zo = true;
@@ -1043,7 +1052,7 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     if (a->algo == AAR_ALGO_NVLS && a->push_chunks > 0 && !kp.zc_src)
       kp.nvls_chunks = kp.sym.cpb - a->push_chunks > 0 ? kp.sym.cpb - a->push_chunks : 0;
     const bool hybrid = a->algo == AAR_ALGO_NVLS && kp.nvls_chunks < kp.sym.cpb;
-    int ws = (kp.zc_src && !hybrid) ? 0 : (kp.zc_src ? 3 : 5), wc = spec ? 1 : (kp.zc_out && a->counts[0] == nullptr ? 1 : 5);
+    int ws = ((kp.zc_src && !hybrid) || a->op == AAR_OP_ALL_GATHER) ? 0 : (kp.zc_src ? 3 : 5), wc = spec ? 1 : (kp.zc_out && a->counts[0] == nullptr ? 1 : 5);
     if (a->role_s > 0 && ws > 0) ws = a->role_s;   // (experiments: AAR_ROLE_S / AAR_ROLE_C warps per CTA)
     if (a->role_c > 0) wc = a->role_c;
     if (ws + wc > kWarps - 2) return fail(AAR_EINVAL, "role_s + role_c leave fewer than 2 of the 16 warps of a CTA for the reduce phase");
@@ -1076,6 +1085,7 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     // data warps 0.156 ms — a system-scope fence per chunk in the middle of the stream costs more than the
     // publisher's scan latency saves; NVLS stages locally (gpu-scope fences), where the data warps win.
     kp.self_publish = a->self_publish == 2 ? 1 : (a->self_publish == 1 ? 0 : (a->algo == AAR_ALGO_NVLS ? 1 : 0));
+    if (a->op != AAR_OP_ALLREDUCE) kp.self_publish = 1;  // (the publisher warp only knows the full round's flag set)
     return 0;
   }
   const int unit_elems = 16 / (in_bytes > wb ? in_bytes : wb);

@@ -341,7 +341,7 @@ __device__ void poller_warp(const KParams& p, const Ctx& c) {
       if (idx < entries) {
         o = idx / cpb;
         const int ch = idx % cpb;
-        exists = ch < p.nch[o];
+        exists = ch < p.nch[o] && (p.a.op != AAR_OP_REDUCE_SCATTER || o == c.rank);  // (a reduce-scatter ends with my own block)
         if (exists) {
           const uint64_t f = ld_volatile64(rflag + idx);
           present = static_cast<uint32_t>(f >> 32) == c.tag;

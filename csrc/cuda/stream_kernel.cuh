@@ -71,9 +71,11 @@ __device__ __forceinline__ void warp_copy_tile(const uint4* __restrict__ s, uint
 }
 
 // NVLS: the switch sums every rank's staging slot on the way in and replicates the result on the way out.
+// `bcast`: the destination is a multicast address too (allreduce); else an ordinary local one (reduce-scatter).
 template <typename TW>
-__device__ __forceinline__ void warp_nvls_tile(const uint4* __restrict__ mc_src, uint4* __restrict__ mc_dst, int units,
-                                               float post, int lane) {
+__device__ __forceinline__ void warp_nvls_tile(const uint4* __restrict__ mc_src, uint4* __restrict__ dst, int units,
+                                               float post, bool bcast, int lane) {
+  uint4* const mc_dst = dst;
   constexpr int U = 8;
   int u0 = lane;
   for (; u0 + 32 * (U - 1) < units; u0 += 32 * U) {  // full sweeps: U switch requests in flight per lane
@@ -81,11 +83,17 @@ __device__ __forceinline__ void warp_nvls_tile(const uint4* __restrict__ mc_src,
 #pragma unroll
     for (int j = 0; j < U; ++j) r[j] = multimem_ld_reduce_add<TW>(mc_src + u0 + 32 * j);
 #pragma unroll
-    for (int j = 0; j < U; ++j) multimem_st(mc_dst + u0 + 32 * j, post != 1.f ? scale_unit<TW>(r[j], post) : r[j]);
+    for (int j = 0; j < U; ++j) {
+      const uint4 v = post != 1.f ? scale_unit<TW>(r[j], post) : r[j];
+      if (bcast) multimem_st(mc_dst + u0 + 32 * j, v);
+      else dst[u0 + 32 * j] = v;
+    }
   }
   for (; u0 < units; u0 += 32) {
     const uint4 r = multimem_ld_reduce_add<TW>(mc_src + u0);
-    multimem_st(mc_dst + u0, post != 1.f ? scale_unit<TW>(r, post) : r);
+    const uint4 v = post != 1.f ? scale_unit<TW>(r, post) : r;
+    if (bcast) multimem_st(mc_dst + u0, v);
+    else dst[u0] = v;
   }
 }
 
@@ -160,6 +168,32 @@ __device__ __forceinline__ void warp_reduce_units(const KParams& p, const Ctx& c
   for (; u0 + 32 * (UB - 1) < units; u0 += 32 * UB) sweep(u0, UB);
   if (UB > 1)
     for (; u0 < units; u0 += 32) sweep(u0, 1);
+}
+
+// All-gather half on its own: my block goes from the caller's tensor straight into every destination's sink row
+// (ReduceBlock with a single contributor).
+__device__ __forceinline__ void warp_bcast_tile(const KParams& p, const Ctx& c, const uint4* __restrict__ src, int64_t sink_off,
+                                                int units, uint32_t dest_ok, uint4* mc_dst, int lane) {
+  constexpr int U = 4;
+  auto put = [&](int u, const uint4& v) {
+    if (mc_dst != nullptr) {
+      multimem_st(mc_dst + u, v);
+    } else {
+      for (int i = 0; i < c.P; ++i) {
+        const int q = (i + c.rank) % c.P;
+        if ((dest_ok >> q) & 1u) reinterpret_cast<uint4*>(p.a.sym[q] + sink_off)[u] = v;
+      }
+    }
+  };
+  int u0 = lane;
+  for (; u0 + 32 * (U - 1) < units; u0 += 32 * U) {
+    uint4 r[U];
+#pragma unroll
+    for (int j = 0; j < U; ++j) r[j] = ld_stream(src + u0 + 32 * j);
+#pragma unroll
+    for (int j = 0; j < U; ++j) put(u0 + 32 * j, r[j]);
+  }
+  for (; u0 < units; u0 += 32) put(u0, ld_stream(src + u0));
 }
 
 // Contributor counts of `n` consecutive elements (n % 4 == 0, 16-byte aligned): bulk stores out of the
@@ -346,7 +380,8 @@ __device__ __noinline__ void reduce_item(const KParams& p, const Ctx& c, const W
   if (off >= ce) return;
   const int len = static_cast<int>(min(static_cast<int64_t>(p.part_r), ce - off));
   const uint64_t w0 = w.wait_r != nullptr ? globaltimer_ns() : 0;
-  const uint32_t mask = wait_chunk_mask(p, c, ch, w.lane);
+  // (an all-gather has nothing to wait for: the block is the caller's, the only contributor is this rank)
+  const uint32_t mask = p.a.op == AAR_OP_ALL_GATHER ? (1u << c.rank) : wait_chunk_mask(p, c, ch, w.lane);
   if (w.wait_r != nullptr) {
     const uint64_t w1 = globaltimer_ns();
     *w.wait_r += w1 - w0;
@@ -358,16 +393,25 @@ __device__ __noinline__ void reduce_item(const KParams& p, const Ctx& c, const W
   const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
   const int64_t sink_off = p.sym.off_sink + (p.sym.sink_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
   const bool push_ch = !kNvls || ch >= p.nvls_chunks;
-  uint4* mc_dst = (w.mc != nullptr && w.dest_ok == all && (!push_ch || p.a.mc_bcast)) ? reinterpret_cast<uint4*>(w.mc + sink_off) : nullptr;
-  if (!push_ch && mask == all && mc_dst != nullptr) {
+  // who gets the reduced tile: every peer this launch may push to — or, in a reduce-scatter, nobody but me
+  const uint32_t bdest = p.a.op == AAR_OP_REDUCE_SCATTER ? (1u << c.rank) : w.dest_ok;
+  uint4* mc_dst = (w.mc != nullptr && bdest == all && (!push_ch || p.a.mc_bcast || p.a.op == AAR_OP_ALL_GATHER))
+                      ? reinterpret_cast<uint4*>(w.mc + sink_off) : nullptr;
+  if (p.a.op == AAR_OP_ALL_GATHER) {
+    const uint4* from = reinterpret_cast<const uint4*>(static_cast<const TW*>(p.a.src[c.vr]) + off);
+    warp_bcast_tile(p, c, from, sink_off, len / E, bdest, mc_dst, w.lane);
+  } else if (!push_ch && mask == all && w.mc != nullptr && (mc_dst != nullptr || p.a.op == AAR_OP_REDUCE_SCATTER)) {
+    // in-switch reduction; the result goes to every rank's sink row through the switch again, or — reduce-scatter
+    // — into my own sink row only
     const int64_t so = p.sym.off_scat + (p.sym.scat_elem(c.slot, c.rank) + off) * static_cast<int64_t>(sizeof(TW));
-    warp_nvls_tile<TW>(reinterpret_cast<const uint4*>(w.mc + so), mc_dst, len / E, post, w.lane);
+    uint4* dst = mc_dst != nullptr ? mc_dst : reinterpret_cast<uint4*>(c.my_sym + sink_off);
+    warp_nvls_tile<TW>(reinterpret_cast<const uint4*>(w.mc + so), dst, len / E, post, mc_dst != nullptr, w.lane);
   } else if (push_ch) {  // contributions were pushed into my own scat rows
-    if (c.P == 1) warp_reduce_units<TW, 4, false>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
-    else if (c.P == 2) warp_reduce_units<TW, 2, false>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
-    else warp_reduce_units<TW, 1, false>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
+    if (c.P == 1) warp_reduce_units<TW, 4, false>(p, c, off, len / E, mask, bdest, mc_dst, post, w.lane);
+    else if (c.P == 2) warp_reduce_units<TW, 2, false>(p, c, off, len / E, mask, bdest, mc_dst, post, w.lane);
+    else warp_reduce_units<TW, 1, false>(p, c, off, len / E, mask, bdest, mc_dst, post, w.lane);
   } else {  // NVLS chunk that closed short of all P contributors: unicast pulls from the peers' staging slots
-    warp_reduce_units<TW, 1, true>(p, c, off, len / E, mask, w.dest_ok, mc_dst, post, w.lane);
+    warp_reduce_units<TW, 1, true>(p, c, off, len / E, mask, bdest, mc_dst, post, w.lane);
   }
   __syncwarp();
   if (w.lane == 0) {
@@ -384,12 +428,12 @@ __device__ __noinline__ void reduce_item(const KParams& p, const Ctx& c, const W
       if (p.a.fast_fences) __threadfence();
       else __threadfence_system();
       const uint64_t f = (static_cast<uint64_t>(c.tag) << 32) | static_cast<uint32_t>(cnt_mask_popc);
-      if (w.mc != nullptr && w.dest_ok == all && !p.a.fast_fences) {
+      if (w.mc != nullptr && bdest == all && !p.a.fast_fences) {
         multimem_st_u64(reinterpret_cast<uint64_t*>(w.mc + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
       } else {
         for (int i = 0; i < c.P; ++i) {
           const int q = (i + c.rank) % c.P;
-          if ((w.dest_ok >> q) & 1u)
+          if ((bdest >> q) & 1u)
             st_relaxed_sys(reinterpret_cast<uint64_t*>(p.a.sym[q] + p.sym.off_rflag) + p.sym.arr_index(c.slot, c.rank, ch), f);
         }
       }
@@ -405,11 +449,12 @@ __device__ __noinline__ bool complete_item(const KParams& p, const Ctx& c, const
   constexpr int E = 16 / sizeof(TW);
   const int64_t bsize = p.part.size(o);
   if (ch < 0 || ch >= p.nch[o]) return false;
+  if (p.a.op == AAR_OP_REDUCE_SCATTER && o != c.rank) return false;  // out holds my block only
   const int64_t cb = chunk_begin(ch, p.a.max_chunk, bsize), ce = chunk_end(ch, p.a.max_chunk, bsize);
   const int64_t off = cb + static_cast<int64_t>(t) * p.part_c;
   if (off >= ce) return false;
   const int len = static_cast<int>(min(static_cast<int64_t>(p.part_c), ce - off));
-  const int64_t g = p.part.start(o) + off;
+  const int64_t g = (p.a.op == AAR_OP_REDUCE_SCATTER ? 0 : p.part.start(o)) + off;
   int32_t* counts = p.a.counts[c.vr];
   if (p.spec_counts && !repair) return warp_fill_counts(counts + g, len, c.P, w.cnt_tile, c.P, w.use_tma, w.lane);
   const uint64_t w0 = w.wait_c != nullptr ? globaltimer_ns() : 0;
@@ -482,7 +527,7 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
   w.first_r = tracer ? &first_r : nullptr;
   bool bulk = false;
   if (role == 0) {
-    if (!p.zc_src || p.nvls_chunks < cpb) {
+    if ((!p.zc_src || p.nvls_chunks < cpb) && p.a.op != AAR_OP_ALL_GATHER) {
       const int per_chunk = P * p.tpc_s, total = per_chunk * cpb;
       for (int it = rw; it < total; it += stride) {
         const int ch = it / per_chunk, rem = it - ch * per_chunk;

@@ -18,6 +18,12 @@ extern "C" {
 enum { AAR_OK = 0, AAR_EINVAL = -1, AAR_ECUDA = -2, AAR_EUNSUPPORTED = -3, AAR_ETOOBIG = -4 };
 enum { AAR_F32 = 0, AAR_BF16 = 1 };
 enum { AAR_ALGO_TWOSHOT = 0, AAR_ALGO_ONESHOT = 1, AAR_ALGO_NVLS = 2 };
+/* The round is a reduce-scatter (AllreduceWorker.scala:212-238 scatter + ScatteredDataBuffer.scala:20-32 reduce)
+ * followed by an all-gather (AllreduceWorker.scala:252-268 broadcast + ReducedDataBuffer.scala:26-53 flush); each half
+ * can be run on its own (stream kernel only):
+ *   AAR_OP_REDUCE_SCATTER  src = the whole message, out / counts = THIS rank's block only (block-sized buffers)
+ *   AAR_OP_ALL_GATHER      src = THIS rank's block, out / counts = the whole message (count 1 where a block arrived) */
+enum { AAR_OP_ALLREDUCE = 0, AAR_OP_REDUCE_SCATTER = 1, AAR_OP_ALL_GATHER = 2 };
 
 /* One fused scatter -> reduce -> broadcast round (reference hot path: AllreduceWorker.scala:
  * 212-238 scatter, ScatteredDataBuffer.scala:20-32 reduce, AllreduceWorker.scala:252-268
@@ -28,6 +34,7 @@ enum { AAR_ALGO_TWOSHOT = 0, AAR_ALGO_ONESHOT = 1, AAR_ALGO_NVLS = 2 };
 typedef struct AarLaunch {
   int32_t rank, world, emu;
   int32_t algo;             /* AAR_ALGO_* */
+  int32_t op;               /* AAR_OP_*: the whole round, or one of its halves */
   int32_t in_dtype;         /* dtype of src and out: AAR_F32 | AAR_BF16 */
   int32_t wire_dtype;       /* dtype of the symmetric slots */
   int32_t ctas;             /* work CTAs per rank (one control CTA is added); clamped to aar_max_ctas() */

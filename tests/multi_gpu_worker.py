@@ -92,6 +92,41 @@ def main() -> int:
                   f"kernel={'stream' if eng.launcher.stream_expected else 'generic'}", flush=True)
         eng.close()
 
+    # --- the two halves of the round on their own: reduce_scatter, all_gather, and the two chained = allreduce
+    n = 1 << 20
+    for algo in ("twoshot", "nvls"):
+        try:
+            eng = DeviceAllreduce(rank, world, n, 1 << 16, max_lag=1, device=local, uds_dir=default_uds_dir(),
+                                  timeout_ms=20_000, algo=algo, kernel="stream")
+        except Exception as e:
+            if algo == "nvls" and "multicast" in str(e):
+                continue
+            raise
+        lo, hi = eng.block_range()
+        blk = torch.empty(hi - lo, device=dev)
+        bcnt = torch.empty(hi - lo, dtype=torch.int32, device=dev)
+        out = torch.empty(n, device=dev)
+        cnt = torch.empty(n, dtype=torch.int32, device=dev)
+        for r in range(4):
+            all_src = srcs_for(n, torch.float32, 40 + r)
+            want = torch.zeros(n)
+            for s in all_src:
+                want += s
+            eng.reduce_scatter(all_src[rank].to(dev), blk, bcnt)
+            torch.cuda.synchronize()
+            ok = torch.allclose(blk.cpu(), want[lo:hi], rtol=1e-5, atol=1e-5) and bool((bcnt == world).all())
+            check(f"reduce_scatter {algo} r={r}", ok)
+            eng.all_gather(blk, out, cnt)
+            torch.cuda.synchronize()
+            check(f"all_gather {algo} r={r}", torch.allclose(out.cpu(), want, rtol=1e-5, atol=1e-5) and bool((cnt == 1).all()))
+        eng.allreduce(all_src[rank].to(dev), out, cnt)   # the ring is still good for whole rounds
+        torch.cuda.synchronize()
+        check(f"allreduce after halves {algo}", torch.allclose(out.cpu(), want, rtol=1e-5, atol=1e-5) and bool((cnt == world).all()))
+        check(f"no timeouts halves {algo}", eng.timeouts_seen() == 0)
+        if rank == 0:
+            print(f"ok reduce_scatter / all_gather algo={eng.algo}", flush=True)
+        eng.close()
+
     # --- bf16 wire
     n = 1 << 20
     for kernel in ("stream", "generic"):

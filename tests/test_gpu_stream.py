@@ -144,3 +144,22 @@ def test_dead_peer_is_not_waited_for(kernel, algo):
         else:
             assert torch.equal(outs[i][:lo], part[:lo]) and bool((counts[i][:lo] == 3).all())
             assert bool((outs[i][lo:] == 0).all()) and bool((counts[i][lo:] == 0).all())
+
+
+def test_all_gather_half_round():
+    """The broadcast half on its own (AllreduceWorker.scala:252-268): every rank's block lands in everybody's output,
+    count 1; then ordinary allreduce rounds keep working on the same ring."""
+    from akka_allreduce_b200.ops import cuda as K
+
+    world, n = 4, 1 << 16
+    cl = _cluster(world, n, 1 << 12, max_lag=1, kernel="stream")
+    full = _srcs(world, n, torch.float32, 1)
+    for r in range(3):
+        blocks = [full[i][cl.geo.start(i):cl.geo.end(i)].contiguous() + r for i in range(world)]
+        outs, counts = cl.run_round(blocks, op=K.OP_ALL_GATHER)
+        want = torch.cat(blocks)
+        for i in range(world):
+            assert torch.equal(outs[i], want) and bool((counts[i] == 1).all())
+    outs, counts = cl.run_round(full)
+    assert torch.equal(outs[0], _ref_sum(full)) and bool((counts[0] == world).all())
+    assert cl.timeouts_seen() == [0] * world
