@@ -12,8 +12,8 @@ from .. import build as _build
 
 MAX_RANKS = 16
 F32, BF16 = 0, 1
-ALGO_TWOSHOT, ALGO_ONESHOT, ALGO_NVLS = 0, 1, 2
-ALGO_NAMES = {"twoshot": ALGO_TWOSHOT, "oneshot": ALGO_ONESHOT, "nvls": ALGO_NVLS}
+ALGO_TWOSHOT, ALGO_ONESHOT, ALGO_NVLS, ALGO_DIRECT = 0, 1, 2, 3
+ALGO_NAMES = {"twoshot": ALGO_TWOSHOT, "oneshot": ALGO_ONESHOT, "nvls": ALGO_NVLS, "direct": ALGO_DIRECT}
 OP_ALLREDUCE, OP_REDUCE_SCATTER, OP_ALL_GATHER = 0, 1, 2
 KERNEL_AUTO, KERNEL_GENERIC, KERNEL_STREAM = 0, 1, 2
 KERNEL_NAMES = {"auto": KERNEL_AUTO, "generic": KERNEL_GENERIC, "stream": KERNEL_STREAM}

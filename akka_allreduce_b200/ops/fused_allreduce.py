@@ -80,7 +80,7 @@ class RoundLauncher:
         self.ctas = ctas or default_ctas(geo.n * torch.empty((), dtype=dtype).element_size(), self.stream_expected)
         # one-shot flavour: 0 push (default), 1 pull with in-switch reduce, 2 pull with unicast loads (opt-in:
         # written after the round's multi-GPU budget was spent, validated in emulation only — see DESIGN.md 7)
-        self.oneshot_pull = int(os.environ.get("AAR_ONESHOT_PULL", 0))
+        self.oneshot_pull = int(os.environ.get("AAR_ONESHOT_PULL", -1))   # -1: the engine picks (pull with NVLS)
         self._prepared: set[int] = set()   # launch structs (by id) whose static fields are filled
         self._injected: set[int] = set()   # launch structs that still carry last round's straggler injection
 
@@ -96,7 +96,7 @@ class RoundLauncher:
         # On for messages of 512 MB and more.  AAR_OVERLAP=1/0 forces it.
         ov = os.environ.get("AAR_OVERLAP")
         a.overlap_flush = int(ov) if ov in ("0", "1") else (1 if g.n * (2 if self.wire_dtype == torch.bfloat16 else 4) >= (512 << 20) else 0)
-        a.oneshot_pull = self.oneshot_pull
+        a.oneshot_pull = max(0, self.oneshot_pull)
         a.kernel, a.mc_bcast = self.kernel, self.mc_bcast
         a.self_publish = int(os.environ.get("AAR_SELF_PUBLISH", 0))
         a.push_chunks = int(os.environ.get("AAR_PUSH_CHUNKS", 0))
@@ -159,11 +159,11 @@ class EmulatedCluster:
         self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
         wire = wire_dtype or dtype
         lib = K.lib()
-        if algo not in ("twoshot", "oneshot"):
-            raise ValueError("the emulated cluster runs the two-shot and one-shot kernels (NVLS needs real peers)")
+        if algo not in ("twoshot", "oneshot", "direct"):
+            raise ValueError("the emulated cluster runs the two-shot, one-shot and direct kernels (NVLS needs real peers)")
         self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
                                       ctas, timeout_ms, scale, normalize,
-                                      os_cap=n if algo == "oneshot" else 0, algo=K.ALGO_NAMES[algo], kernel=kernel)
+                                      os_cap=n if algo in ("oneshot", "direct") else 0, algo=K.ALGO_NAMES[algo], kernel=kernel)
         L = self.launcher
         # all ranks share this GPU: (ctas + 1) x world CTAs must be resident at once
         cap = K.check(lib.aar_max_ctas(K.KERNEL_STREAM if L.stream_expected else K.KERNEL_GENERIC, world,

@@ -58,18 +58,29 @@ class DeviceAllreduce:
         self.geo = Geometry.make(n, max_chunk, world, max_lag, align_blocks)
         wire = wire_dtype or dtype
         elem = torch.empty((), dtype=dtype).element_size()
-        if algo not in ("auto", "twoshot", "nvls", "oneshot"):
+        if algo not in ("auto", "twoshot", "nvls", "oneshot", "direct"):
             raise ValueError(f"unknown algo {algo!r}")
         # One-shot (every rank sums all P copies itself) is the latency path for small messages; it needs
         # thresholds of 1 (ranks reduce independently, so they must all see the same contributors).
         oneshot_ok = oneshot_eligible(self.geo, th_reduce, th_complete, max_lag, th_allreduce)
-        # crossover measured on B200s (profiles/sweep_*): one hop wins up to 1 MB on 2-4 GPUs, 512 KB on 8
-        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", (1 << 20) if world <= 4 else (512 << 10)))
-        if algo == "oneshot" and not oneshot_ok:
-            raise K.AarError("algo=oneshot needs thReduce = thComplete = 1 and maxLag >= 1 (or the thAllreduce gate)")
+        # crossover measured on B200s (profiles/sweep_*): with the pull form (one multimem.ld_reduce per 16 bytes of
+        # the P staged copies) one hop wins up to 1 MB on 8 GPUs and 2 MB on 2-4
+        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", (2 << 20) if world <= 4 else (1 << 20)))
+        if algo in ("oneshot", "direct") and not oneshot_ok:
+            raise K.AarError(f"algo={algo} needs thReduce = thComplete = 1 and maxLag >= 1 (or the thAllreduce gate)")
         use_oneshot = algo == "oneshot" or (algo == "auto" and oneshot_ok and small and world > 1)
+        # Direct: the one-shot idea streamed chunk by chunk for LARGE messages on two ranks — same bytes on the link
+        # as two-shot (N each way), one hop instead of two.  Costs a second message-sized row per ring slot.
+        align = 16 // elem
+        direct_ok = (oneshot_ok and world == 2 and wire == dtype and scale == 1.0 and n % align == 0
+                     and (max_chunk % align == 0 or max_chunk >= n) and self.geo.step % align == 0)
+        if algo == "direct" and not direct_ok:
+            raise K.AarError("algo=direct needs two ranks, thresholds 1, dtype == wire dtype and 16-byte aligned sizes")
+        use_direct = algo == "direct" or (algo == "auto" and direct_ok and not use_oneshot
+                                           and os.environ.get("AAR_NO_DIRECT") is None)
         self.launcher = RoundLauncher(self.geo, dtype, wire, th_reduce, th_complete, th_allreduce,
-                                      ctas, timeout_ms, scale, normalize, os_cap=n if use_oneshot else 0, kernel=kernel)
+                                      ctas, timeout_ms, scale, normalize, os_cap=n if (use_oneshot or use_direct) else 0,
+                                      kernel=kernel)
         lib = self.launcher.lib
         # every CTA of a launch must be resident: the generic kernel fits one per SM, the stream kernel two
         cap = K.check(lib.aar_max_ctas(K.KERNEL_STREAM if self.launcher.stream_expected else K.KERNEL_GENERIC, 1,
@@ -93,6 +104,10 @@ class DeviceAllreduce:
             raise K.AarError("algo=nvls needs a multicast alias (NVLS), world > 1 and thReduce = 1")
         if use_oneshot:
             self.algo = "oneshot"
+            if self.launcher.oneshot_pull < 0:  # stage locally, let the switch sum the P staged copies on the way in
+                self.launcher.oneshot_pull = 1 if self.mc_ptr else 0
+        elif use_direct:
+            self.algo = "direct"
         elif algo == "nvls" or (algo == "auto" and nvls_ok and os.environ.get("AAR_NO_NVLS") is None):
             self.algo = "nvls"
         else:
@@ -207,7 +222,7 @@ class DeviceAllreduce:
 
     def _half_round(self, op: int, src: torch.Tensor, out: torch.Tensor, counts: torch.Tensor | None,
                     stream: torch.cuda.Stream | None) -> None:
-        if self.algo == "oneshot" or not self.launcher.stream_expected:
+        if self.algo in ("oneshot", "direct") or not self.launcher.stream_expected:
             raise K.AarError("reduce_scatter / all_gather need the stream kernel: aligned blocks (align_blocks=True), "
                              "dtype == wire dtype, and a two-shot or NVLS engine (algo != oneshot)")
         a = self._launch

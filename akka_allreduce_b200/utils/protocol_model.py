@@ -53,10 +53,10 @@ class ModelConfig:
                                # launch, i.e. before the gate and without the destination mask
     output_view: bool = False  # zero-copy output (`output_view`): the caller keeps reading round r's sink slot until it
                                # launches round r+L (the worker loop delivers sink(r) before that launch)
-    notices: bool = False      # skip notices (implemented in csrc/host/shm_cluster.cc, a candidate for the kernel): a sender
+    notices: bool = False      # skip notices (csrc/cuda/round_common.cuh decide_dest_mask_warp / peers_gone, csrc/host/shm_cluster.cc): a sender
                                # that leaves a peer out records the tag in a per-(dest, src) word outside the slot ring,
                                # and a waiter treats "not arrived + notice >= my tag" as "will never arrive"
-    oneshot_backpressure: bool = False  # the one-shot kernel as it is has NO destination mask;
+    oneshot_backpressure: bool = False  # True = the shipped one-shot kernel (destination mask in its prologue); False = the round-1 kernel without it;
                                         # True models the planned fix (same `done + L >= tag` rule as two-shot)
 
 

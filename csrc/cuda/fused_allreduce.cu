@@ -913,13 +913,16 @@ int launch_stream(const KParams& kp, cudaStream_t stream) {
 
 template <typename TIn, typename TW>
 int launch_oneshot(const KParams& kp, cudaStream_t stream) {
-  int nct = static_cast<int>(ceil_div(kp.a.n, 4096));
-  if (nct > kp.a.ctas) nct = kp.a.ctas;
+  int nct = static_cast<int>(ceil_div(kp.a.n, 4096));  // one CTA per 4096 elements, as many as the flag array holds (`ctas` is for the two-shot kernels)
   if (nct > kMaxOneShotCtas) nct = kMaxOneShotCtas;
-  if (nct < 1) nct = 1;
-  dim3 grid(nct, kp.a.emu ? kp.a.world : 1);
-  cudaError_t e;
   auto* fn = kp.a.oneshot_pull ? aar_oneshot_kernel<TIn, TW, true> : aar_oneshot_kernel<TIn, TW, false>;
+  int resident = 0;  // CTAs wait for their peers' CTAs: all of them (of every emulated rank) must be resident
+  if (int rc = resident_ctas(fn, 0, &resident)) return rc;
+  const int ranks_here = kp.a.emu ? kp.a.world : 1;
+  if (nct > resident / ranks_here) nct = resident / ranks_here;
+  if (nct < 1) nct = 1;
+  dim3 grid(nct, ranks_here);
+  cudaError_t e;
   if (kp.a.emu) {
     void* args[] = {const_cast<KParams*>(&kp)};
     e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(fn), grid, dim3(kThreads), args, 0, stream);
@@ -964,6 +967,7 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   kp.zc_src = kp.zc_out = kp.spec_counts = 0;
   kp.warps_s = kp.warps_r = 0;
   kp.self_publish = 0;
+  kp.msg_chunks = 0;
   kp.nvls_chunks = a->algo == AAR_ALGO_NVLS ? kp.sym.cpb : 0;
   kp.n_s = kp.n_r = kp.n_c = 0;
   const int in_bytes = a->in_dtype == AAR_BF16 ? 2 : 4;
@@ -990,6 +994,14 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     // every rank sums the copies it holds on its own: only with all contributions required do the ranks agree
     if (a->req_reduce < a->world || a->req_complete < kp.total_chunks)
       return fail(AAR_EINVAL, "one-shot needs thReduce = thComplete = 1 (ranks reduce independently)");
+  } else if (a->algo == AAR_ALGO_DIRECT) {
+    if (a->world != 2) return fail(AAR_EINVAL, "the direct algorithm is for two ranks (it moves (P-1) x N per rank)");
+    if (a->n > a->os_cap) return fail(AAR_ETOOBIG, "message larger than the one-shot capacity of the region (direct needs os_cap >= n)");
+    if (a->L < 2 && a->gate_count <= 0)
+      return fail(AAR_EINVAL, "direct needs maxLag >= 1 or the thAllreduce gate (a peer could overwrite a row in use)");
+    if (a->req_reduce < a->world || a->req_complete < kp.total_chunks)
+      return fail(AAR_EINVAL, "direct needs thReduce = thComplete = 1 (ranks reduce independently)");
+    if (a->op != AAR_OP_ALLREDUCE) return fail(AAR_EUNSUPPORTED, "direct runs whole rounds only");
   } else if (a->algo != AAR_ALGO_TWOSHOT) {
     return fail(AAR_EUNSUPPORTED, "unknown algorithm");
   }
@@ -999,6 +1011,8 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   if (a->kernel == 2 && !stream_ok)
     return fail(AAR_EINVAL, "the stream kernel needs 16-byte aligned pointers, block step and chunk size, and src dtype == wire dtype");
   use_stream = stream_ok && a->kernel != 1;
+  if (a->algo == AAR_ALGO_DIRECT && (!use_stream || a->n % align_elems != 0))
+    return fail(AAR_EUNSUPPORTED, "direct runs on the stream kernel only (aligned buffers and message length, src dtype == wire dtype)");
   if (a->op != AAR_OP_ALLREDUCE) {
     if (!use_stream) return fail(AAR_EUNSUPPORTED, "reduce-scatter / all-gather rounds run on the stream kernel only (aligned buffers, src dtype == wire dtype, not one-shot)");
     if (a->op == AAR_OP_REDUCE_SCATTER) {  // the round ends with my own block: its chunks always get reduced
@@ -1009,7 +1023,7 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   }
 
   // Zero-copy: the caller's tensors ARE this round's staging / sink slots (real ranks only).
-  if (!a->emu && a->algo != AAR_ALGO_ONESHOT && in_bytes == wb && a->op == AAR_OP_ALLREDUCE) {
+  if (!a->emu && a->algo != AAR_ALGO_ONESHOT && a->algo != AAR_ALGO_DIRECT && in_bytes == wb && a->op == AAR_OP_ALLREDUCE) {
     const uint8_t* src = static_cast<const uint8_t*>(a->src[0]);
     const uint8_t* out = static_cast<const uint8_t*>(a->out[0]);
     bool zs = a->scale == 1.0f, zo = true;
@@ -1038,6 +1052,38 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   }
   const int64_t chunk_len = a->max_chunk < kp.sym.block ? a->max_chunk : (kp.sym.block > 0 ? kp.sym.block : 1);
   if (chunk_len >= (int64_t{1} << 31)) return fail(AAR_ETOOBIG, "chunks of 2^31 elements or more: use a smaller maxChunkSize");
+  if (use_stream && a->algo == AAR_ALGO_DIRECT) {
+    // Two roles: push my message to the peer, sum "mine + the peer's" into the output.  Chunks are those of the
+    // whole message; nothing is reduced by an owner, so there are no ReduceBlock flags and nothing to complete.
+    const int64_t mlen = a->max_chunk < a->n ? a->max_chunk : a->n;
+    kp.msg_chunks = static_cast<int>(ceil_div(a->n, a->max_chunk));
+    if (kp.msg_chunks > 2 * kp.sym.cpb) return fail(AAR_EINVAL, "direct: more message chunks than flag words");
+    for (int r = 0; r < kMaxRanks; ++r) kp.nch[r] = 0;
+    kp.total_chunks = 0;
+    kp.a.req_complete = 0;
+    int ws = a->role_s > 0 ? a->role_s : 6;
+    if (ws > kWarps - 2) ws = kWarps - 2;
+    kp.warps_s = ws;
+    kp.warps_r = kWarps - ws;
+    const int64_t sweep = 32 * (16 / wb);
+    const int64_t cap = a->part_sc_kb > 0 ? (static_cast<int64_t>(a->part_sc_kb) << 10) / wb : 16 * sweep;
+    auto tile_of = [&](int role_warps, int& part, int& tpc) {
+      const int64_t warps = static_cast<int64_t>(kp.a.ctas) * role_warps;
+      int64_t t = ceil_div(ceil_div(a->n, 2 * warps), sweep) * sweep;
+      if (t < 4 * sweep) t = 4 * sweep;
+      if (t > cap) t = ceil_div(cap, sweep) * sweep;
+      const int64_t whole = ceil_div(mlen, sweep) * sweep;
+      if (t > whole) t = whole;
+      part = static_cast<int>(t);
+      tpc = static_cast<int>(ceil_div(mlen, t));
+    };
+    tile_of(kp.warps_s, kp.part_s, kp.tpc_s);
+    tile_of(kp.warps_r, kp.part_r, kp.tpc_r);
+    kp.part_c = kp.part_r;
+    kp.tpc_c = 0;
+    kp.self_publish = a->self_publish == 2 ? 1 : 0;  // default: the publisher warp batches the chunk flags
+    return 0;
+  }
   if (use_stream) {
     // Warps of every CTA are split between the three phases by what each has to move.  Scatter and completion are
     // copies (HBM, or NVLink egress for the push scatter); reduce+broadcast is the NVLink-bound part and gets the
@@ -1058,6 +1104,10 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     if (ws + wc > kWarps - 2) return fail(AAR_EINVAL, "role_s + role_c leave fewer than 2 of the 16 warps of a CTA for the reduce phase");
     kp.warps_s = ws;
     kp.warps_r = kWarps - ws - wc;
+    // Measured on 8 GPUs: with 15 reduce warps per CTA a 1 GB round takes 3.35 ms, with 6 (the ordinary-tensor
+    // split) 2.32 ms; 256 MB 0.69 vs 0.65 ms; 64 MB and below the other way round (0.180 vs 0.196 ms).  Thousands of
+    // warps, each on its own tile, spread the in-flight multimem requests over more pages than the TLBs reach.
+    if (static_cast<int64_t>(a->n) * wb >= (int64_t{128} << 20) && kp.warps_r > 6 && a->role_s <= 0 && a->role_c <= 0) kp.warps_r = 6;
     // Warp tiles: about two items per warp of the phase's role, between 4 and 64 warp sweeps (2-32 KB) each; flags
     // stay per chunk, a self-resetting counter tells the publisher when the last tile of a chunk is in.
     const int64_t sweep = 32 * (16 / wb);

@@ -36,6 +36,7 @@ struct KParams {
   int zc_src;         // the source IS this round's staging slot: phase S moves nothing, only raises flags
   int zc_out;         // the output IS this round's sink slot: phase C writes only the contributor counts
   int spec_counts;    // stream kernel: counts are written as P up front and repaired if a chunk came short
+  int msg_chunks;     // direct mode: chunks of the whole message (flags are per message chunk there)
   int nvls_chunks;    // NVLS: leading chunks of every block that go through the switch; the rest take the unicast push path
   int self_publish;   // stream kernel: data warps raise their own flags, the publisher warp only sends the zero-copy ones
   int warps_s, warps_r;  // stream kernel: warps per CTA that scatter / reduce+broadcast (the rest complete)
@@ -73,6 +74,18 @@ __device__ __forceinline__ uint32_t all_ranks_mask(int P) { return P >= 32 ? 0xf
 // parts of `part` elements a chunk of `len` elements is cut into (both < 2^31: checked on the host)
 __device__ __forceinline__ uint32_t parts_of(int64_t len, int part) {
   return (static_cast<uint32_t>(len) + static_cast<uint32_t>(part) - 1u) / static_cast<uint32_t>(part);
+}
+
+// Direct mode keeps one u32 arrival flag per (slot, sender, message chunk); it borrows the ReduceBlock flag area,
+// which that mode does not use otherwise (2 x cpb words per (slot, sender): enough for the chunks of a whole
+// message on two ranks).
+__device__ __forceinline__ uint32_t* direct_flag(const KParams& p, uint8_t* region, int slot, int src, int m) {
+  return reinterpret_cast<uint32_t*>(region + p.sym.off_rflag) + (static_cast<int64_t>(slot) * p.sym.P + src) * (2 * p.sym.cpb) + m;
+}
+__device__ __forceinline__ int64_t msg_chunk_len(const KParams& p, int m) {
+  const int64_t lo = static_cast<int64_t>(m) * p.a.max_chunk;
+  const int64_t hi = lo + p.a.max_chunk < p.a.n ? lo + p.a.max_chunk : p.a.n;
+  return hi - lo;
 }
 
 __device__ __forceinline__ void note_timeout(const Ctx& c) {
@@ -252,7 +265,9 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
         bool ready = false;
         if (e < s_entries) {  // ScatterBlock (d, ch): all parts out?
           const int d = e / cpb, ch = e % cpb;
-          if (!p.zc_src || ch >= p.nvls_chunks) {
+          if (p.a.algo == AAR_ALGO_DIRECT) {  // entry e = message chunk e, pushed to every peer
+            if (e < p.msg_chunks) ready = ld_volatile(scat_cnt + e) == parts_of(msg_chunk_len(p, e), p.part_s);
+          } else if (!p.zc_src || ch >= p.nvls_chunks) {
             const int64_t bs = p.part.size(d);
             if (ch < p.nch[d]) {
               const uint32_t want = parts_of(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s);
@@ -286,7 +301,12 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
       for (int w = 0; w < kPubWords; ++w) {
         if (!((mine >> w) & 1u)) continue;
         const int e = base0 + 32 * w + lane;
-        if (e < s_entries) {
+        if (e < s_entries && p.a.algo == AAR_ALGO_DIRECT) {
+          const uint32_t dest_ok = ld_volatile(fin + 1) & ~kDecided;
+          st_volatile(scat_cnt + e, 0u);
+          for (int q = 0; q < P; ++q)
+            if (q != c.rank && ((dest_ok >> q) & 1u)) st_relaxed_sys(direct_flag(p, p.a.sym[q], c.slot, c.rank, e), c.tag);
+        } else if (e < s_entries) {
           const int d = e / cpb, ch = e % cpb;
           st_volatile(scat_cnt + e, 0u);
           st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);

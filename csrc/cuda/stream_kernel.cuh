@@ -470,6 +470,126 @@ __device__ __noinline__ bool complete_item(const KParams& p, const Ctx& c, const
   return warp_fill_counts(counts + g, len, present ? cnt : 0, w.cnt_tile, c.P, w.use_tma && !repair, w.lane);
 }
 
+// ---------------------------------------------------------------- direct mode (two ranks, large messages)
+// Push: tile t of message chunk m -> every peer's one-shot row [me], source scale fused.
+template <typename TW>
+__device__ __noinline__ void direct_push_item(const KParams& p, const Ctx& c, const WarpEnv& w, int m, int t) {
+  constexpr int E = 16 / sizeof(TW);
+  const int64_t clen = msg_chunk_len(p, m);
+  const int64_t off = static_cast<int64_t>(t) * p.part_s;
+  if (off >= clen || w.muted) return;
+  const int len = static_cast<int>(min(static_cast<int64_t>(p.part_s), clen - off));
+  const int64_t g = static_cast<int64_t>(m) * p.a.max_chunk + off;
+  const TW* from = static_cast<const TW*>(p.a.src[c.vr]) + g;
+  for (int i = 1; i < c.P; ++i) {
+    const int q = (i + c.rank) % c.P;
+    if (((w.skip >> q) & 1u) || !((w.dest_ok >> q) & 1u)) continue;
+    TW* dst = reinterpret_cast<TW*>(p.a.sym[q] + p.sym.off_os) + p.sym.os_elem(c.slot, c.rank) + g;
+    warp_copy_tile<TW>(reinterpret_cast<const uint4*>(from), reinterpret_cast<uint4*>(dst), len / E, p.a.scale, w.lane);
+  }
+  __syncwarp();
+  if (w.lane == 0) {
+    __threadfence();
+    uint32_t* cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt) + m;
+    if (!p.self_publish) {
+      atomicAdd(cnt, 1u);  // the publisher warp raises the chunk's flag
+    } else if (atomicAdd(cnt, 1u) + 1u == parts_of(clen, p.part_s)) {
+      st_volatile(cnt, 0u);
+      if (p.a.fast_fences) __threadfence();
+      else __threadfence_system();
+      for (int q = 0; q < c.P; ++q)
+        if (q != c.rank && !((w.skip >> q) & 1u) && ((w.dest_ok >> q) & 1u))
+          st_relaxed_sys(direct_flag(p, p.a.sym[q], c.slot, c.rank, m), c.tag);
+    }
+  }
+}
+
+// Sum: out[tile] = sum over the ranks whose chunk m has landed (mine is the source itself), rank order, fp32.
+template <typename TW>
+__device__ __noinline__ bool direct_sum_item(const KParams& p, const Ctx& c, const WarpEnv& w, int m, int t) {
+  constexpr int E = 16 / sizeof(TW);
+  using U = Unit<TW, E>;
+  const int64_t clen = msg_chunk_len(p, m);
+  const int64_t off = static_cast<int64_t>(t) * p.part_r;
+  if (off >= clen) return false;
+  const int len = static_cast<int>(min(static_cast<int64_t>(p.part_r), clen - off));
+  const int64_t g = static_cast<int64_t>(m) * p.a.max_chunk + off;
+  const int P = c.P, lane = w.lane;
+  // wait for every peer's chunk (or for word that it will not come)
+  const uint64_t w0 = w.wait_r != nullptr ? globaltimer_ns() : 0;
+  const uint32_t all = all_ranks_mask(P);
+  uint32_t have = w.muted ? 0u : (1u << c.rank);
+  {
+    const uint32_t* f = lane < P ? direct_flag(p, c.my_sym, c.slot, lane, m) : nullptr;
+    int spins = 0;
+    for (;;) {
+      have |= __ballot_sync(0xffffffffu, lane < P && lane != c.rank && ld_volatile(f) == c.tag);
+      if ((have | (1u << c.rank)) == all) break;
+      if ((++spins & (kSlowPoll - 1)) == 0) {
+        const uint32_t gone = peers_gone(p, c) & ~have;
+        if (gone != 0 && ((have | gone | (1u << c.rank)) == all)) {
+          have |= __ballot_sync(0xffffffffu, lane < P && lane != c.rank && ld_volatile(f) == c.tag);
+          break;
+        }
+        if (__shfl_sync(0xffffffffu, (lane == 0 && give_up_now(c, c.deadline)) ? 1 : 0, 0) != 0) break;
+      }
+      __nanosleep(64);
+    }
+    if (lane < P && lane != c.rank && ((have >> lane) & 1u)) (void)ld_acquire_sys(f);  // acquire: the sender's data
+    __syncwarp();
+  }
+  if (w.wait_r != nullptr) {
+    const uint64_t w1 = globaltimer_ns();
+    *w.wait_r += w1 - w0;
+    if (*w.first_r == 0) *w.first_r = w1;
+  }
+  const int cnt = __popc(have);
+  const float post = (p.a.normalize && cnt > 0) ? 1.f / static_cast<float>(cnt) : 1.f;
+  const uint4* mine = reinterpret_cast<const uint4*>(static_cast<const TW*>(p.a.src[c.vr]) + g);
+  uint4* out = reinterpret_cast<uint4*>(static_cast<TW*>(p.a.out[c.vr]) + g);
+  const int units = len / E;
+  constexpr int UB = 4;  // units per lane and sweep: with two ranks, eight 16-byte loads in flight
+  auto sweep = [&](int u0, int nb) {
+    float acc[UB][E];
+#pragma unroll
+    for (int b = 0; b < UB; ++b)
+#pragma unroll
+      for (int e = 0; e < E; ++e) acc[b][e] = 0.f;
+    for (int s = 0; s < P; ++s) {
+      if (!((have >> s) & 1u)) continue;
+      const uint4* row = s == c.rank ? mine
+                                     : reinterpret_cast<const uint4*>(reinterpret_cast<const TW*>(c.my_sym + p.sym.off_os) + p.sym.os_elem(c.slot, s) + g);
+      uint4 r[UB];
+#pragma unroll
+      for (int b = 0; b < UB; ++b) r[b] = make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+      for (int b = 0; b < UB; ++b)
+        if (b < nb) r[b] = s == c.rank ? ld_stream(row + u0 + 32 * b) : ld_fresh(row + u0 + 32 * b);
+#pragma unroll
+      for (int b = 0; b < UB; ++b) {
+        float v[E];
+        U::unpack(r[b], v);
+        const float sc = s == c.rank ? p.a.scale : 1.f;  // (the peers' copies were scaled on the way out)
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[b][e] += v[e] * sc;
+      }
+    }
+#pragma unroll
+    for (int b = 0; b < UB; ++b)
+      if (b < nb) {
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[b][e] *= post;
+        out[u0 + 32 * b] = U::pack(acc[b]);
+      }
+  };
+  int u0 = lane;
+  for (; u0 + 32 * (UB - 1) < units; u0 += 32 * UB) sweep(u0, UB);
+  for (; u0 < units; u0 += 32) sweep(u0, 1);
+  int32_t* counts = p.a.counts[c.vr];
+  if (counts == nullptr) return false;
+  return warp_fill_counts(counts + g, len, cnt, w.cnt_tile, P, w.use_tma, lane);
+}
+
 // ---------------------------------------------------------------- the kernel
 template <typename TW, bool kNvls>
 __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_constant__ KParams p) {
@@ -526,7 +646,15 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
   w.wait_c = tracer ? &wait_c : nullptr;
   w.first_r = tracer ? &first_r : nullptr;
   bool bulk = false;
-  if (role == 0) {
+  if (p.a.algo == AAR_ALGO_DIRECT) {
+    if (role == 0) {
+      const int total = p.msg_chunks * p.tpc_s;
+      for (int it = rw; it < total; it += stride) direct_push_item<TW>(p, c, w, it / p.tpc_s, it % p.tpc_s);
+    } else if (role == 1) {
+      const int total = p.msg_chunks * p.tpc_r;
+      for (int it = rw; it < total; it += stride) bulk |= direct_sum_item<TW>(p, c, w, it / p.tpc_r, it % p.tpc_r);
+    }
+  } else if (role == 0) {
     if ((!p.zc_src || p.nvls_chunks < cpb) && p.a.op != AAR_OP_ALL_GATHER) {
       const int per_chunk = P * p.tpc_s, total = per_chunk * cpb;
       for (int it = rw; it < total; it += stride) {

@@ -12,7 +12,7 @@
 //   notice[P] u32             skip notices: notice[s] = highest tag for which peer s left ME out of its
 //                             scatter and broadcast (back-pressure); lets a wait give up without the clock
 //   os    [L][P][os_cap]      one-shot path (small messages): every peer's WHOLE message
-//   os_arr[L][P][16] u32      one-shot arrival tags, one per (sender, CTA slice)
+//   os_arr[L][P][64] u32      one-shot arrival tags, one per (sender, CTA slice)
 //
 // L = maxLag + 1 ring slots, slot = round % L (buffer/AllReduceBuffer.scala:34-42); P = peers;
 // cpb = chunks per block.  A message is a store into the destination's region followed by a
@@ -26,7 +26,7 @@ namespace aar {
 
 constexpr int kMaxRanks = 16;       // one NVSwitch domain
 constexpr int kAlignElems = 128;    // block padding, in elements (keeps every block 512 B aligned)
-constexpr int kMaxOneShotCtas = 16; // one-shot: every CTA owns a slice and its own arrival flags
+constexpr int kMaxOneShotCtas = 64; // one-shot: every CTA owns a slice and its own arrival flags
 
 struct SymLayout {
   int P, L;

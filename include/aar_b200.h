@@ -17,7 +17,12 @@ extern "C" {
 
 enum { AAR_OK = 0, AAR_EINVAL = -1, AAR_ECUDA = -2, AAR_EUNSUPPORTED = -3, AAR_ETOOBIG = -4 };
 enum { AAR_F32 = 0, AAR_BF16 = 1 };
-enum { AAR_ALGO_TWOSHOT = 0, AAR_ALGO_ONESHOT = 1, AAR_ALGO_NVLS = 2 };
+/* AAR_ALGO_DIRECT: the one-shot idea for LARGE messages on two ranks (stream kernel).  With P = 2 a two-shot round and
+ * a one-shot round put the same number of bytes on the link (N each way), but the one-shot form has one hop instead
+ * of two: every rank streams its whole message into the peer's one-shot row chunk by chunk while the other warps sum
+ * "mine + the peer's" for every chunk that has landed, straight into the output.  Needs thresholds of 1, world = 2,
+ * a region laid out with os_cap >= n. */
+enum { AAR_ALGO_TWOSHOT = 0, AAR_ALGO_ONESHOT = 1, AAR_ALGO_NVLS = 2, AAR_ALGO_DIRECT = 3 };
 /* The round is a reduce-scatter (AllreduceWorker.scala:212-238 scatter + ScatteredDataBuffer.scala:20-32 reduce)
  * followed by an all-gather (AllreduceWorker.scala:252-268 broadcast + ReducedDataBuffer.scala:26-53 flush); each half
  * can be run on its own (stream kernel only):

@@ -16,13 +16,13 @@ rows = [
  ("thresholds 2/3, <= 2 timeouts, 3 ranks", ModelConfig(P=3, L=2, rounds=2, req_reduce=2, req_complete=2, gate_count=2, timeouts=True, giveups=2), {}),
  ("seeded bug: no back-pressure", ModelConfig(P=2, L=2, rounds=4, req_reduce=1, req_complete=1, gate_count=1, timeouts=True, backpressure=False), {}),
  ("thresholds 2/3, no timeouts (liveness)", ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2), {}),
- ("same with skip notices", ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2, notices=True), {}),
+ ("same with skip notices (shipped kernels)", ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2, notices=True), {}),
  ("one slot, no gate, skip notices", ModelConfig(P=2, L=1, rounds=4, notices=True), {}),
  ("one-shot, 2 slots", ModelConfig(P=3, L=2, rounds=3, oneshot=True), {}),
  ("one-shot, 1 slot, no gate (refused by the ABI)", ModelConfig(P=2, L=1, rounds=3, oneshot=True), {}),
- ("one-shot under timeouts (known gap)", ModelConfig(P=2, L=2, rounds=4, oneshot=True, timeouts=True), {}),
- ("one-shot under timeouts with the planned mask", ModelConfig(P=2, L=2, rounds=5, oneshot=True, timeouts=True, oneshot_backpressure=True), {}),
- ("input_view, thReduce 1, thComplete 2/3", ModelConfig(P=3, L=2, rounds=3, early_write=True, req_complete=2), {}),
+ ("one-shot under timeouts WITHOUT a destination mask (the round-1 kernel: seeded bug)", ModelConfig(P=2, L=2, rounds=4, oneshot=True, timeouts=True), {}),
+ ("one-shot under timeouts, shipped kernel (destination mask + notices)", ModelConfig(P=2, L=2, rounds=5, oneshot=True, timeouts=True, oneshot_backpressure=True), {}),
+ ("input_view written after round r-1, thReduce 1, thComplete 2/3 (the library hands the view out only with thresholds 1)", ModelConfig(P=3, L=2, rounds=3, early_write=True, req_complete=2), {}),
  ("input_view, thReduce 0.5", ModelConfig(P=2, L=3, rounds=5, early_write=True, req_reduce=1, req_complete=1), {}),
  ("output_view, thresholds 1", ModelConfig(P=3, L=2, rounds=4, output_view=True), {}),
  ("output_view, thReduce 2/3 (now refused)", ModelConfig(P=3, L=2, rounds=4, output_view=True, req_reduce=2), {}),

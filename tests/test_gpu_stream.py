@@ -163,3 +163,32 @@ def test_all_gather_half_round():
     outs, counts = cl.run_round(full)
     assert torch.equal(outs[0], _ref_sum(full)) and bool((counts[0] == world).all())
     assert cl.timeouts_seen() == [0] * world
+
+
+@pytest.mark.parametrize("n,mc,max_lag", [(1 << 20, 1 << 16, 1), (1 << 18, 1 << 18, 2), (5 * 4096 + 512, 4096, 1)])
+def test_direct_two_ranks(n, mc, max_lag):
+    """Direct (streamed one-shot for two ranks): push my message to the peer chunk by chunk, sum mine + the peer's
+    straight into the output; bit-identical to the two-shot result (same rank order)."""
+    world = 2
+    cl = _cluster(world, n, mc, max_lag=max_lag, timeout_ms=5000, algo="direct")
+    assert cl.kernel_used() == "stream"
+    for r in range(2 * (max_lag + 1) + 1):
+        srcs = _srcs(world, n, torch.float32, r)
+        outs, counts = cl.run_round(srcs)
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i], want), f"round {r} rank {i}: max err {(outs[i] - want).abs().max()}"
+            assert bool((counts[i] == world).all())
+    assert cl.timeouts_seen() == [0] * world
+    assert cl.done_tags() == [cl.round] * world
+
+
+def test_direct_peer_that_never_shows_up():
+    """A muted peer: the round closes on the clock with the rank's own data and count 1."""
+    from akka_allreduce_b200.ops.fused_allreduce import Injection
+
+    cl = _cluster(2, 1 << 14, 1 << 12, timeout_ms=20, algo="direct")
+    srcs = _srcs(2, 1 << 14, torch.float32, 4)
+    outs, counts = cl.run_round(srcs, Injection(mute=0b10))
+    assert torch.equal(outs[0], srcs[0]) and bool((counts[0] == 1).all())
+    assert torch.equal(outs[1], srcs[0]) and bool((counts[1] == 1).all())   # the muted rank still hears its peer
