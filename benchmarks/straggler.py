@@ -107,16 +107,23 @@ def distributed(args) -> dict:
         state["last"] = state["t1"] = now
         state["done"] += 1
         if out.iteration % args.check_every == 0:
-            bits = out.data.to(torch.int64)
-            bad = (bits.to(out.data.dtype) != out.data) | (bits < 0) | (bits >= (1 << world))
-            pop = lut[bits.clamp(0, (1 << world) - 1)]
-            bad |= pop != out.count
-            acc[0] += bad.sum()
-            acc[1] += (out.count == 0).sum()
-            acc[2] += out.count.numel()
-            torch.minimum(min_count, out.count.min().reshape(1), out=min_count)
-            if out.iteration % 16 == 0:       # contributor-count histogram, sampled
-                hist.add_(torch.bincount(out.count, minlength=world + 1)[: world + 1])
+            verify(out.data, out.count, out.iteration % 16 == 0)
+
+    def verify(data, count, sample_hist):
+        bits = data.to(torch.int32)
+        inb = bits & ((1 << world) - 1)
+        bad = (inb.to(data.dtype) != data) | (lut[inb] != count)     # value = bit mask of exactly `count` contributors
+        acc[0] += bad.sum()
+        acc[1] += (count == 0).sum()
+        acc[2] += count.numel()
+        torch.minimum(min_count, count.min().reshape(1), out=min_count)
+        if sample_hist:       # contributor-count histogram, sampled
+            hist.add_(torch.bincount(count, minlength=world + 1)[: world + 1])
+
+    # first use of these ops loads their kernels (tens of ms): do it now, not inside round 0 on every rank at once
+    verify(torch.zeros(1024, device=dev), torch.zeros(1024, dtype=torch.int32, device=dev), True)
+    acc.zero_(); hist.zero_(); min_count.fill_(99)
+    torch.cuda.synchronize()
 
     w = DeviceWorker(source, sink, cfg, master_port=cfg.cluster.port, device=local)
     dist.barrier()

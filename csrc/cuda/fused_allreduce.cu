@@ -1008,7 +1008,7 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   if (a->op < AAR_OP_ALLREDUCE || a->op > AAR_OP_ALL_GATHER) return fail(AAR_EINVAL, "op must be AAR_OP_ALLREDUCE, _REDUCE_SCATTER or _ALL_GATHER");
   if (a->kernel < 0 || a->kernel > 2) return fail(AAR_EINVAL, "kernel must be 0 (auto), 1 (generic) or 2 (stream)");
   const bool stream_ok = vec && a->in_dtype == a->wire_dtype && a->algo != AAR_ALGO_ONESHOT;
-  if (a->kernel == 2 && !stream_ok)
+  if (a->kernel == 2 && !stream_ok && a->algo != AAR_ALGO_ONESHOT)  // (the one-shot kernel is its own: `kernel` does not apply)
     return fail(AAR_EINVAL, "the stream kernel needs 16-byte aligned pointers, block step and chunk size, and src dtype == wire dtype");
   use_stream = stream_ok && a->kernel != 1;
   if (a->algo == AAR_ALGO_DIRECT && (!use_stream || a->n % align_elems != 0))
@@ -1061,7 +1061,9 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
     for (int r = 0; r < kMaxRanks; ++r) kp.nch[r] = 0;
     kp.total_chunks = 0;
     kp.a.req_complete = 0;
-    int ws = a->role_s > 0 ? a->role_s : 6;
+    // (2 GPUs, 64 MB: 2-3 pushing warps per CTA 0.148 ms, 4: 0.150, 6: 0.162, 8: 0.170 — the link is full long before
+    // the SMs are; more pushers only add contention)
+    int ws = a->role_s > 0 ? a->role_s : 3;
     if (ws > kWarps - 2) ws = kWarps - 2;
     kp.warps_s = ws;
     kp.warps_r = kWarps - ws;

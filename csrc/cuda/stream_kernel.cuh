@@ -12,7 +12,9 @@
 //     reduce warp waits only for its chunk's ScatterBlock flags, a completion warp only for its chunk's
 //     ReduceBlock flag, so no wait can hold up work that is ready, the round is pipelined chunk by chunk
 //     (the HBM-bound copies of one chunk overlap the NVLink-bound reduce of another) and there is no cycle
-//     of waits.  Within a role, tiles are dealt chunk-major, round-robin over all CTAs.  (A first version
+//     of waits.  Within a role, tiles are dealt chunk-major, round-robin over all CTAs — statically: handing
+//     them out through one ticket counter per kind (so that warps of an exhausted role could help the others)
+//     was measured on one GPU at 0.169 ms against 0.104 ms; thousands of warps on three counters serialise.  (A first version
 //     interleaved the three kinds in one list per warp; a blocked reduce item then delayed the scatter
 //     item behind it, and the delays chained from wave to wave: 0.205 ms for one GPU's 64 MB against
 //     0.123 ms for the generic kernel.)

@@ -66,9 +66,10 @@ def main() -> int:
     if bad:
         print(f"[rank {rank}] FAIL sums do not match counts in rounds {bad[:8]}", flush=True)
         return 1
-    # the tail of the job ran without the victim: count P-1 on the survivors' blocks, 0 on the victim's
+    # the tail of the job ran without the victim: count P-1 on the survivors' blocks, 0 on the victim's (nobody
+    # reduces it) — or P-1 everywhere when the algorithm has no owners (one-shot / direct: every rank sums what it holds)
     tail = [seen[r] for r in range(rounds - 50, rounds)]
-    if not all(v[2] == 0 and v[3] == world - 1 for v in tail):
+    if not all(v[2] in (0, world - 1) and v[3] == world - 1 for v in tail):
         print(f"[rank {rank}] FAIL tail counts {[(v[2], v[3]) for v in tail[:5]]}", flush=True)
         return 1
     tail_s = (seen[rounds - 1][0] - seen[rounds - 51][0]) / 50

@@ -192,3 +192,30 @@ def test_direct_peer_that_never_shows_up():
     outs, counts = cl.run_round(srcs, Injection(mute=0b10))
     assert torch.equal(outs[0], srcs[0]) and bool((counts[0] == 1).all())
     assert torch.equal(outs[1], srcs[0]) and bool((counts[1] == 1).all())   # the muted rank still hears its peer
+
+
+@pytest.mark.parametrize("kernel,algo,world,n,mc,align", [
+    ("stream", "twoshot", 4, 1 << 14, 1 << 11, False), ("generic", "twoshot", 4, 1 << 14, 1 << 11, False),
+    ("stream", "twoshot", 3, 3 * 4096 + 1024, 1000, True), ("generic", "twoshot", 4, 778, 3, False),
+    (None, "oneshot", 4, 5000, 4096, False), ("stream", "direct", 2, 5 * 4096 + 512, 4096, False),
+])
+def test_no_write_outside_the_callers_buffers(kernel, algo, world, n, mc, align):
+    """Guard bands around every output and count buffer stay untouched and the sources are not modified (the pool's
+    compute-sanitizer is closed: this is the bounds check the suite can make on its own)."""
+    G = 1024
+    cl = _cluster(world, n, mc, max_lag=1, timeout_ms=5000, kernel=kernel, algo=algo, align_blocks=align)
+    big_o = [torch.full((n + 2 * G,), -777.0, device="cuda:0") for _ in range(world)]
+    big_c = [torch.full((n + 2 * G,), -777, dtype=torch.int32, device="cuda:0") for _ in range(world)]
+    outs = [b[G:G + n] for b in big_o]
+    cnts = [b[G:G + n] for b in big_c]
+    for r in range(3):
+        srcs = _srcs(world, n, torch.float32, r)
+        keep = [s.clone() for s in srcs]
+        cl.run_round(srcs, outs=outs, counts=cnts)
+        torch.cuda.synchronize()
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i], want) and bool((cnts[i] == world).all())
+            assert bool((big_o[i][:G] == -777.0).all()) and bool((big_o[i][G + n:] == -777.0).all())
+            assert bool((big_c[i][:G] == -777).all()) and bool((big_c[i][G + n:] == -777).all())
+            assert torch.equal(srcs[i], keep[i])
