@@ -243,7 +243,8 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
         for (int e = lane; e < s_entries; e += 32) {
           const int d = e / cpb, ch = e % cpb;
           if (((skip >> d) & 1u) || !((dest_ok >> d) & 1u)) continue;
-          if (ch >= p.nch[d] || ch >= p.nvls_chunks) continue;  // (push chunks are flagged by whoever scatters them)
+          if (ch >= p.nch[d]) continue;
+          if (p.a.algo == AAR_ALGO_NVLS && ch >= p.nvls_chunks) continue;  // (a hybrid round's push chunks are flagged by whoever scatters them)
           st_relaxed_sys(reinterpret_cast<uint32_t*>(p.a.sym[d] + p.sym.off_arr) + p.sym.arr_index(c.slot, c.rank, ch), c.tag);
         }
       }
@@ -267,7 +268,7 @@ __device__ void publisher_warp(const KParams& p, const Ctx& c) {
           const int d = e / cpb, ch = e % cpb;
           if (p.a.algo == AAR_ALGO_DIRECT) {  // entry e = message chunk e, pushed to every peer
             if (e < p.msg_chunks) ready = ld_volatile(scat_cnt + e) == parts_of(msg_chunk_len(p, e), p.part_s);
-          } else if (!p.zc_src || ch >= p.nvls_chunks) {
+          } else if (!p.zc_src || (p.a.algo == AAR_ALGO_NVLS && ch >= p.nvls_chunks)) {
             const int64_t bs = p.part.size(d);
             if (ch < p.nch[d]) {
               const uint32_t want = parts_of(chunk_end(ch, p.a.max_chunk, bs) - chunk_begin(ch, p.a.max_chunk, bs), p.part_s);

@@ -657,7 +657,7 @@ __global__ void __launch_bounds__(kThreads, 2) aar_stream_kernel(const __grid_co
       for (int it = rw; it < total; it += stride) bulk |= direct_sum_item<TW>(p, c, w, it / p.tpc_r, it % p.tpc_r);
     }
   } else if (role == 0) {
-    if ((!p.zc_src || p.nvls_chunks < cpb) && p.a.op != AAR_OP_ALL_GATHER) {
+    if ((!p.zc_src || (kNvls && p.nvls_chunks < cpb)) && p.a.op != AAR_OP_ALL_GATHER) {
       const int per_chunk = P * p.tpc_s, total = per_chunk * cpb;
       for (int it = rw; it < total; it += stride) {
         const int ch = it / per_chunk, rem = it - ch * per_chunk;

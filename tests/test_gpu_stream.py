@@ -219,3 +219,33 @@ def test_no_write_outside_the_callers_buffers(kernel, algo, world, n, mc, align)
             assert bool((big_o[i][:G] == -777.0).all()) and bool((big_o[i][G + n:] == -777.0).all())
             assert bool((big_c[i][:G] == -777).all()) and bool((big_c[i][G + n:] == -777).all())
             assert torch.equal(srcs[i], keep[i])
+
+
+def test_single_rank_engine_with_registered_buffers():
+    """One real rank (no emulation): ordinary tensors, then source and sink aliased to the engine's own slots — the
+    zero-copy path raises its ScatterBlock flags from the publisher warp at launch (nothing is scattered)."""
+    import tempfile
+
+    from akka_allreduce_b200.parallel.engine import DeviceAllreduce
+
+    n = 1 << 20
+    eng = DeviceAllreduce(0, 1, n, 1 << 16, max_lag=1, th_allreduce=1.0, device=0, uds_dir=tempfile.mkdtemp(),
+                          timeout_ms=2000)
+    try:
+        src = torch.randn(n, device="cuda:0")
+        out = torch.empty_like(src)
+        cnt = torch.empty(n, dtype=torch.int32, device="cuda:0")
+        for r in range(3):
+            eng.allreduce(src + r, out, cnt)
+            torch.cuda.synchronize()
+            assert torch.equal(out, src + r) and bool((cnt == 1).all())
+        for r in range(5):
+            iv, ov = eng.input_view(eng.round), eng.output_view(eng.round)
+            assert iv is not None and ov is not None
+            iv.copy_(src * (r + 2))
+            eng.allreduce(iv, ov, cnt)
+            torch.cuda.synchronize()
+            assert torch.equal(ov, src * (r + 2)) and bool((cnt == 1).all())
+        assert eng.timeouts_seen() == 0
+    finally:
+        eng.close()
