@@ -63,9 +63,10 @@ class DeviceAllreduce:
         # One-shot (every rank sums all P copies itself) is the latency path for small messages; it needs
         # thresholds of 1 (ranks reduce independently, so they must all see the same contributors).
         oneshot_ok = oneshot_eligible(self.geo, th_reduce, th_complete, max_lag, th_allreduce)
-        # crossover measured on B200s (profiles/sweep_*): with the pull form (one multimem.ld_reduce per 16 bytes of
-        # the P staged copies) one hop wins up to 1 MB on 8 GPUs and 2 MB on 2-4
-        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", (2 << 20) if world <= 4 else (1 << 20)))
+        # crossover measured on B200s (profiles/raw/sweep_8gpu_oneshot_*): with the pull form (one multimem.ld_reduce
+        # per 16 bytes of the P staged copies) one hop beats the NVLS two-shot round up to 2 MB on 8 GPUs (44 vs 54 us
+        # at 2 MB, 69 vs 55 us at 4 MB) and on 2-4 GPUs
+        small = n * elem <= int(os.environ.get("AAR_ONESHOT_BYTES", 2 << 20))
         if algo in ("oneshot", "direct") and not oneshot_ok:
             raise K.AarError(f"algo={algo} needs thReduce = thComplete = 1 and maxLag >= 1 (or the thAllreduce gate)")
         use_oneshot = algo == "oneshot" or (algo == "auto" and oneshot_ok and small and world > 1)
