@@ -35,15 +35,16 @@ def sass():
         for pat in pats:
             row[pat] = sum(1 for i in ins if pat in i)
         rows.append(row)
-        if "aar_twoshot_kernel<float, float, true>" in dem:
-            listing = (dem, ins)
+        if "aar_stream_kernel<float, true>" in dem:  # the headline kernel: full listing, addresses + operands
+            body = [re.sub(r"\s*/\* 0x[0-9a-f]{16} \*/\s*$", "", l).rstrip() for l in p.split("\n")[1:]]
+            listing = (dem, [l for l in body if l.strip()])
     with open(os.path.join(OUT, "sass_evidence.md"), "w") as f:
         f.write("# SASS evidence (cuobjdump -sass akka_allreduce_b200/_native/libaar_cuda.so, sm_100a)\n\n")
         f.write("What the mnemonics prove: `UBLKCP.*` = TMA bulk copies (`cp.async.bulk`) staging tiles global->shared->global "
                 "(the store side also targets peer GPUs); `SYNCS.ARRIVE.TRANS64` / `SYNCS.PHASECHK...TRYWAIT` = mbarrier "
                 "expect_tx / try_wait; `LDGMC.E.ADD.F32x4` / `LDGMC.E.HPADD.BF16` = `multimem.ld_reduce` (sum inside the NVSwitch; the matching "
                 "`multimem.st` is emitted as `STG.E.128.STRONG.SYS` on the multicast alias, right after the LDGMC group in "
-                "fused_allreduce_f32_nvls.sass); "
+                "stream_kernel_f32_nvls.sass); in the stream kernel `UBLKCP.G.S` is the TMA fill of the per-element counts; "
                 "`*.STRONG.SYS` loads/stores = flag traffic and peer-visible data; `MEMBAR.SC.SYS` only in the publisher warp / "
                 "finish path.  No HMMA/UTC*MMA anywhere: the path has no GEMM, so tcgen05/TMEM is not used (north star).\n\n")
         keys = ["kernel", "instructions"] + pats
@@ -51,8 +52,11 @@ def sass():
         for r in rows:
             f.write("| " + " | ".join(str(r[k]) for k in keys) + " |\n")
     if listing:
-        with open(os.path.join(OUT, "fused_allreduce_f32_nvls.sass"), "w") as f:
-            f.write(f"// {listing[0]}  (mnemonics only; regenerate with scripts/make_profiles.py)\n")
+        with open(os.path.join(OUT, "stream_kernel_f32_nvls.sass"), "w") as f:
+            f.write(f"// cuobjdump -sass akka_allreduce_b200/_native/libaar_cuda.so, function {listing[0]} (sm_100a)\n"
+                    "// (instruction encodings stripped; addresses and operands as printed; regenerate with scripts/make_profiles.py)\n"
+                    "// LDGMC.E.ADD.F32x4 = multimem.ld_reduce, STG.E.128.STRONG.SYS on the multicast alias = multimem.st,\n"
+                    "// UBLKCP = cp.async.bulk (count fill), MEMBAR.SC.SYS / .GPU = fences, LDG.E.STRONG.SYS + CCTL.IVALL = ld.acquire.sys\n")
             f.write("\n".join(listing[1]) + "\n")
 
 
