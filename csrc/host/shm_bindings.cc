@@ -74,6 +74,7 @@ void bind_shm(py::module_& m) {
       .def_property_readonly("next_round", &ShmCluster::next_round)
       .def("issued", &ShmCluster::issued)
       .def("force_complete", &ShmCluster::force_complete)
+      .def("set_dead_peers", &ShmCluster::set_dead_peers, py::arg("rank"), py::arg("mask"))
       .def(
           "run_round",
           [](ShmCluster& c, int round, std::vector<FloatArray> srcs, uint32_t mute_mask, std::vector<uint32_t> skip_dest,

@@ -58,8 +58,8 @@ constexpr size_t kHeaderBytes = 256;
 }  // namespace
 
 size_t ShmCluster::control_bytes() {
-  // header + force[16] + progress[16] + next_round[16] + notice[16*16], rounded to a page
-  return static_cast<size_t>(SymLayout::up(kHeaderBytes + 3 * kMaxRanks * 4 + kMaxRanks * kMaxRanks * 4, 4096));
+  // header + force[16] + progress[16] + next_round[16] + notice[16*16] + dead[16], rounded to a page
+  return static_cast<size_t>(SymLayout::up(kHeaderBytes + 4 * kMaxRanks * 4 + kMaxRanks * kMaxRanks * 4, 4096));
 }
 size_t ShmCluster::region_bytes() const { return static_cast<size_t>(SymLayout::up(sym_.total_bytes, 4096)); }
 
@@ -90,6 +90,8 @@ void ShmCluster::place(uint8_t* block) {
   next_round_ = reinterpret_cast<std::atomic<int>*>(p);
   p += kMaxRanks * 4;
   notice_ = reinterpret_cast<std::atomic<uint32_t>*>(p);
+  p += kMaxRanks * kMaxRanks * 4;
+  dead_ = reinterpret_cast<std::atomic<uint32_t>*>(p);
   regions_.clear();
   for (int r = 0; r < cfg_.world; ++r) regions_.push_back(block + control_bytes() + static_cast<size_t>(r) * region_bytes());
 }
@@ -200,6 +202,11 @@ int ShmCluster::next_round() const {
   return m;
 }
 
+void ShmCluster::set_dead_peers(int rank, uint32_t mask) {
+  if (rank < 0 || rank >= cfg_.world) throw std::invalid_argument("ShmCluster::set_dead_peers: rank out of range");
+  dead_[static_cast<size_t>(rank)].store(mask & ~(1u << rank), std::memory_order_release);
+}
+
 void ShmCluster::force_complete(int rank, int round) {
   if (rank < 0 || rank >= cfg_.world) throw std::invalid_argument("ShmCluster: rank out of range");
   if (round < 0) return;
@@ -245,16 +252,18 @@ ShmRoundInfo ShmCluster::rank_round(int rank, int round, const float* src, float
     for (;;) {
       int have = 0;
       for (int q = 0; q < P; ++q) have += (q == rank || ld_acquire(done + q) + 1u >= tag) ? 1 : 0;
-      if (have >= gate_count_ || expired(1)) break;
+      const int alive = P - __builtin_popcount(dead_[static_cast<size_t>(rank)].load(std::memory_order_acquire) & ((1u << P) - 1u));
+      if (have >= (gate_count_ < alive ? gate_count_ : alive) || expired(1)) break;
       relax(spins);
     }
   }
   const double dbg_gate = std::chrono::duration<double, std::milli>(Clock::now() - t0).count();
   // ---- back-pressure: leave out a peer whose ring slot still holds a round more than maxLag behind
   uint32_t dest_ok = 0;
+  const uint32_t dead_now = dead_[static_cast<size_t>(rank)].load(std::memory_order_acquire);
   for (int q = 0; q < P; ++q) {
     const uint32_t d = q == rank ? tag : ld_acquire(done + q);
-    if (d + static_cast<uint32_t>(L_) >= tag) dest_ok |= 1u << q;
+    if (d + static_cast<uint32_t>(L_) >= tag && !((dead_now >> q) & 1u)) dest_ok |= 1u << q;
   }
   info.dest_mask = dest_ok;
   // ---- skip notices.  A peer left out here will get neither my slices nor my reduced block for this round; without
@@ -264,8 +273,9 @@ ShmRoundInfo ShmCluster::rank_round(int rank, int round, const float* src, float
   // whoever sees notice >= t also sees every flag this rank raised for rounds before the one that wrote it.
   if (cfg_.skip_notice)
     for (int q = 0; q < P; ++q)
-      if (!((dest_ok >> q) & 1u)) notice_[static_cast<size_t>(q) * P + rank].store(tag, std::memory_order_release);
-  auto left_out_by = [&](int s) {  // did rank s tell me that it skipped me for this round (or a later one)?
+      if (!((dest_ok >> q) & 1u) && !((dead_now >> q) & 1u)) notice_[static_cast<size_t>(q) * P + rank].store(tag, std::memory_order_release);
+  auto left_out_by = [&](int s) {  // will nothing come from rank s: it is known dead, or it told me that it skipped me
+    if ((dead_[static_cast<size_t>(rank)].load(std::memory_order_acquire) >> s) & 1u) return true;
     return cfg_.skip_notice && notice_[static_cast<size_t>(rank) * P + s].load(std::memory_order_acquire) >= tag;
   };
 
@@ -399,6 +409,7 @@ ShmRoundInfo ShmCluster::rank_round(int rank, int round, const float* src, float
   // ---- CompleteAllreduce(rank, round) to everyone
   for (int i = 0; i < P; ++i) {
     const int q = (i + rank) % P;
+    if ((dead_now >> q) & 1u) continue;
     st_release(reinterpret_cast<uint32_t*>(region(q) + sym_.off_done) + rank, tag);
   }
   return info;

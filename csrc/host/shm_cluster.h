@@ -98,6 +98,9 @@ class ShmCluster {
   int issued(int rank) const;  // lowest round number `rank` may still issue
 
   void force_complete(int rank, int round);  // waits of rounds <= `round` on `rank` close immediately
+  // Peers `rank` has been told are gone (bit q = rank q; the kernel's dead-peer mask, DeviceAllreduce.set_dead_peers):
+  // nothing is pushed to them, nothing waits for them, and the gate asks for no more than the live ranks can give.
+  void set_dead_peers(int rank, uint32_t mask);
   const SymLayout& layout() const { return sym_; }
   int req_reduce() const { return req_reduce_; }
   int req_complete() const { return req_complete_; }
@@ -125,6 +128,7 @@ class ShmCluster {
   std::atomic<int>* progress_ = nullptr;       // [rank]: round it is working on (free-run catch-up)
   std::atomic<int>* next_round_ = nullptr;     // [rank]: lowest round it may still issue (tags never repeat)
   std::atomic<uint32_t>* notice_ = nullptr;    // [dest][src]: highest tag for which src left dest out
+  std::atomic<uint32_t>* dead_ = nullptr;      // [rank]: peers that rank has been told are gone
 };
 
 }  // namespace aar

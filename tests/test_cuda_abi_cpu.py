@@ -83,3 +83,36 @@ def test_shared_memory_cluster_uses_the_kernels_region_layout(n, mc, P, lag):
     geo = Geometry.make(n, mc, P, lag, False)
     assert (cl.total_chunks, cl.req_reduce, cl.req_complete) == (geo.total_chunks, geo.req_reduce(0.75), geo.req_complete(0.8))
     assert cl.gate_count == gate_count(1.0, P)
+
+
+def _launch(**kw):
+    a = K.AarLaunch()
+    a.world, a.rank, a.n, a.max_chunk, a.L, a.slot, a.tag, a.ctas = 4, 0, 1 << 16, 1 << 12, 2, 0, 1, 8
+    a.req_reduce, a.req_complete = 4, 16
+    for k, v in kw.items():
+        setattr(a, k, v)
+    return a
+
+
+@pytest.mark.parametrize("kw,needle", [
+    (dict(slot=2), "slot"), (dict(slot=-1), "slot"), (dict(rank=4), "rank"), (dict(rank=-1), "rank"),
+    (dict(world=0), "world"), (dict(world=17), "world"), (dict(tag=0), "tag"), (dict(ctas=0), "cta"),
+    (dict(os_cap=-1), "one-shot"), (dict(block_step=1), "block_step"),
+])
+def test_launch_descriptions_are_validated_before_any_cuda_call(kw, needle):
+    """A public C ABI must not turn a bad slot or rank into out-of-bounds stores on a peer (round-1 review): the
+    checks sit in front of everything, so they can be exercised without a GPU."""
+    lib = K.lib()
+    a = _launch(**kw)
+    assert lib.aar_round_kernel(C.byref(a)) == -1                     # AAR_EINVAL
+    assert needle in lib.aar_last_error().decode()
+    assert lib.aar_allreduce_round(C.byref(a), None) == -1
+
+
+def test_scratch_words_the_host_writes():
+    """Force tag and dead-peer mask are device words inside the scratch, next to each other, never reset by a kernel."""
+    lib = K.lib()
+    for n, mc, P in ((1 << 20, 1 << 16, 8), (778, 3, 4)):
+        force, dead, total = (lib.aar_scratch_force_offset(n, mc, P, 0), lib.aar_scratch_dead_offset(n, mc, P, 0),
+                              lib.aar_scratch_bytes(n, mc, P, 0))
+        assert dead == force + 8 and dead + 4 <= total and force % 4 == 0

@@ -173,3 +173,41 @@ def test_replacement_worker_joins_running_job():
         d, cnt = outs[0][r]
         assert (d[cnt > 0] == cnt[cnt > 0]).all()   # sum of ones == contributors
     assert not neww.errors
+
+
+def test_master_announces_removals_when_asked():
+    """Extension for the CUDA backend (MasterConfig.announce_removals): a worker removed from a running job makes the
+    master re-send InitWorkers — a peer-map refresh for the survivors (AllreduceWorker.scala:87-89) — so that GPU
+    workers can stop pushing to and waiting for the dead rank.  Off by default: the reference sends InitWorkers once."""
+    for announce in (False, True):
+        bus = h.LocalBus()
+        c = cfg(total_workers=3, th_allreduce=0.6, max_round=10)
+        c.announce_removals = announce
+        ep, master = bus.add_master(c)
+        probes = [bus.add_probe() for _ in range(3)]
+        for p in probes:
+            master.member_up(p)
+        bus.run()
+        for p in probes:
+            bus.take(p)                                  # the initial InitWorkers + StartAllreduce(0)
+        master.terminated(probes[1])
+        bus.run()
+        got = [bus.take(p) for p in probes]
+        if not announce:
+            assert all(not g for g in got)
+        else:
+            assert not got[1]                            # nothing goes to the removed worker
+            for i in (0, 2):
+                (init,) = got[i]
+                assert isinstance(init, h.InitWorkers) and sorted(init.workers) == [0, 2] and init.worker_num == 3
+                assert init.dest_id == i and init.start_round == 0
+        # before the job has started there is nobody to tell
+        bus2 = h.LocalBus()
+        c2 = cfg(total_workers=3)
+        c2.announce_removals = announce
+        _, m2 = bus2.add_master(c2)
+        p0 = bus2.add_probe()
+        m2.member_up(p0)
+        m2.terminated(p0)
+        bus2.run()
+        assert not bus2.take(p0)

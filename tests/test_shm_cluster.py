@@ -173,3 +173,40 @@ def test_any_shape_matches_plain_sums():
                 assert not infos[r]["timed_out"]
 
     run()
+
+
+def test_dead_peer_is_neither_pushed_to_nor_waited_for():
+    """The kernel's dead-peer mask in the shared-memory form of the protocol: rank 3 never runs; once the others have
+    been told, every threshold is still 1 and the timeout 5 s, yet rounds close at once with count 3 and zeros /
+    count 0 on the dead owner's block (AllreduceMaster.scala:46-52: the master drops the worker, AllreduceWorker.scala:
+    213-216: the others skip it)."""
+    import threading
+    import time
+
+    from akka_allreduce_b200 import host
+
+    c = host.ShmConfig()
+    c.world, c.n, c.max_chunk, c.max_lag = 4, 64, 4, 1
+    c.th_reduce = c.th_complete = 1.0
+    c.th_allreduce, c.timeout_ms = 0.75, 5000.0
+    cl = host.ShmCluster(c)
+    for r in range(3):
+        cl.set_dead_peers(r, 1 << 3)
+    results = {}
+
+    def run(rank):
+        src = np.full(64, float(1 << rank), dtype=np.float32)
+        for rnd in range(6):
+            results[(rank, rnd)] = cl.rank_round(rank, rnd, src)
+
+    t0 = time.perf_counter()
+    threads = [threading.Thread(target=run, args=(r,)) for r in range(3)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(20)
+    assert time.perf_counter() - t0 < 4.0 and len(results) == 18      # nobody sat out the 5 s timeout
+    for (rank, rnd), (out, cnt, info) in results.items():
+        assert not info["timed_out"]
+        assert (out[:48] == 7.0).all() and (cnt[:48] == 3).all()       # 2^0 + 2^1 + 2^2 from exactly three contributors
+        assert (out[48:] == 0.0).all() and (cnt[48:] == 0).all()       # nobody owns block 3 any more
