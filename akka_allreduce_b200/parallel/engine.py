@@ -124,6 +124,7 @@ class DeviceAllreduce:
         self._dead_src = torch.zeros(1, dtype=torch.int32).pin_memory()
         self._ctl_stream = torch.cuda.Stream(device=self.device)
         self.round = 0
+        self._inplace_src: torch.Tensor | None = None   # direct algorithm, in-place calls only
         self._launch = a = K.AarLaunch()
         self.launcher.prepare(a)
         a.rank, a.emu = rank, 0
@@ -197,13 +198,23 @@ class DeviceAllreduce:
             raise ValueError(f"Input data size {src.numel()} is different from initialization time {g.n}!")
         if src.dtype != self.launcher.dtype or out.dtype != self.launcher.dtype:
             raise ValueError("dtype differs from the engine's")
-        if self.partial_thresholds and src.data_ptr() < out.data_ptr() + out.numel() * out.element_size() and \
-                out.data_ptr() < src.data_ptr() + src.numel() * src.element_size():
+        if self.partial_thresholds and self._overlap(src, out):
             # With thresholds of 1 a block of `out` is written only after its owner has received THIS rank's slice
             # of it, so the launch may run in place.  Below 1 the owner can finish without this rank: the result
             # (or the zeros of a missing chunk) could land on source elements that are still to be scattered.
             raise ValueError("allreduce in place (out overlaps src) needs thReduce = thComplete = 1; "
                              "pass a separate output tensor")
+        if self.algo == "direct" and self._overlap(src, out):
+            # In a two-shot round a block of `out` is written only after its owner holds this rank's slice of it; in
+            # a direct round the sum warps write chunk m as soon as the PEER's chunk m has landed, whether or not
+            # this rank's own push of chunk m has read the source yet.  In place (what the DDP hook does) therefore
+            # goes through a private copy of the source, on the launch stream.
+            s = stream if stream is not None else torch.cuda.current_stream(self.device)
+            if self._inplace_src is None:
+                self._inplace_src = torch.empty(g.n, dtype=self.launcher.dtype, device=self.device)
+            with torch.cuda.stream(s):
+                self._inplace_src.copy_(src.reshape(-1), non_blocking=True)
+            src = self._inplace_src
         r = self.round if round_ is None else round_
         a = self._launch
         self.launcher.fill(a, r, inj)
@@ -213,6 +224,11 @@ class DeviceAllreduce:
         self.launcher.launch(a, stream)
         if round_ is None:
             self.round += 1
+
+    @staticmethod
+    def _overlap(x: torch.Tensor, y: torch.Tensor) -> bool:
+        return (x.data_ptr() < y.data_ptr() + y.numel() * y.element_size()
+                and y.data_ptr() < x.data_ptr() + x.numel() * x.element_size())
 
     # ---- the two halves of the round on their own (the scatter->reduce half is a reduce-scatter,
     # the broadcast half an all-gather; AllreduceWorker.scala:212-238 and :252-268) ---------------------------

@@ -339,7 +339,6 @@ __device__ void work_cta(const KParams& p, const Ctx& c) {
   int32_t* counts = p.a.counts[c.vr];
   uint32_t* scat_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_scat_cnt);
   uint32_t* red_cnt = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_cnt);
-  uint32_t* red_mask = reinterpret_cast<uint32_t*>(c.scratch + p.scr.off_red_mask);
   uint64_t* trace = p.a.trace != nullptr
                         ? p.a.trace + (static_cast<int64_t>(c.vr) * (p.a.ctas + 1) + blockIdx.x) * 16
                         : nullptr;
@@ -840,7 +839,6 @@ __global__ void __launch_bounds__(kThreads, 1) aar_oneshot_kernel(const __grid_c
 }
 
 // ---------------------------------------------------------------- host side
-constexpr int kMaxDevices = 64;
 static int wire_bytes_of(int dtype) { return dtype == AAR_BF16 ? 2 : 4; }
 thread_local std::string g_error;
 int fail(int code, const std::string& what) {
