@@ -135,7 +135,8 @@ int aar_allreduce_round(const AarLaunch* launch, void* stream);
  *   <= 3000); beyond that the call fails with AAR_ETOOBIG and a message naming both numbers.
  * - It calls no cudaMalloc/cudaFree and no allocating library routine; the array is cleared with a
  *   cudaMemsetAsync on `stream` before each launch, so nothing carries over from the previous call
- *   (this also means the host-side force tag is always 0 here: rounds close by threshold or timeout).
+ *   (this also means the host-written words inside the scratch — the force tag and the dead-peer mask — are
+ *   always 0 here: rounds close by threshold, skip notice or timeout).
  * - The first call on each device looks the array's device address up (that device must be current);
  *   make that first call before you start capturing any stream.
  * - All calls in the process share the one array per device.  Two rounds that overlap on the GPU
