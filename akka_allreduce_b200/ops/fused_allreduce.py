@@ -75,7 +75,7 @@ class RoundLauncher:
         # the stream kernel needs 16-byte aligned block starts and chunk starts (and aligned tensors, checked per launch)
         align = 16 // min(torch.empty((), dtype=dtype).element_size(), torch.empty((), dtype=wire_dtype).element_size())
         self.stream_expected = (self.kernel != K.KERNEL_GENERIC and dtype == wire_dtype and geo.step % align == 0
-                                and (geo.max_chunk % align == 0 or geo.max_chunk >= geo.step))
+                                and geo.n % align == 0 and (geo.max_chunk % align == 0 or geo.max_chunk >= geo.step))
         # work CTAs per rank; the library clamps it to what the device keeps resident (aar_max_ctas)
         self.ctas = ctas or default_ctas(geo.n * torch.empty((), dtype=dtype).element_size(), self.stream_expected)
         # one-shot flavour: 0 push (default), 1 pull with in-switch reduce, 2 pull with unicast loads (opt-in:

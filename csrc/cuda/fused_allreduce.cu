@@ -1005,9 +1005,12 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   }
   if (a->op < AAR_OP_ALLREDUCE || a->op > AAR_OP_ALL_GATHER) return fail(AAR_EINVAL, "op must be AAR_OP_ALLREDUCE, _REDUCE_SCATTER or _ALL_GATHER");
   if (a->kernel < 0 || a->kernel > 2) return fail(AAR_EINVAL, "kernel must be 0 (auto), 1 (generic) or 2 (stream)");
-  const bool stream_ok = vec && a->in_dtype == a->wire_dtype && a->algo != AAR_ALGO_ONESHOT;
+  // The stream kernel moves whole 16-byte units only: besides aligned block and chunk starts it needs a message
+  // length that is a multiple of the unit (else the last block would end in a partial unit — the generic kernel
+  // has a scalar tail for that).
+  const bool stream_ok = vec && a->n % align_elems == 0 && a->in_dtype == a->wire_dtype && a->algo != AAR_ALGO_ONESHOT;
   if (a->kernel == 2 && !stream_ok && a->algo != AAR_ALGO_ONESHOT)  // (the one-shot kernel is its own: `kernel` does not apply)
-    return fail(AAR_EINVAL, "the stream kernel needs 16-byte aligned pointers, block step and chunk size, and src dtype == wire dtype");
+    return fail(AAR_EINVAL, "the stream kernel needs 16-byte aligned pointers, block step, chunk size and message length, and src dtype == wire dtype");
   use_stream = stream_ok && a->kernel != 1;
   if (a->algo == AAR_ALGO_DIRECT && (!use_stream || a->n % align_elems != 0))
     return fail(AAR_EUNSUPPORTED, "direct runs on the stream kernel only (aligned buffers and message length, src dtype == wire dtype)");

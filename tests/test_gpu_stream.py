@@ -249,3 +249,19 @@ def test_single_rank_engine_with_registered_buffers():
         assert eng.timeouts_seen() == 0
     finally:
         eng.close()
+
+
+def test_message_length_not_a_multiple_of_the_unit_goes_to_the_generic_kernel():
+    """Aligned blocks but a message whose last block ends in a partial 16-byte unit: the stream kernel moves whole
+    units only, so the library must pick the generic kernel (scalar tail) — and the tail must come out right."""
+    world, n = 4, 100003
+    cl = _cluster(world, n, 4096, max_lag=1, timeout_ms=5000, align_blocks=True)
+    assert cl.kernel_used() == "generic"
+    for r in range(3):
+        srcs = _srcs(world, n, torch.float32, r)
+        outs, counts = cl.run_round(srcs)
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i], want) and bool((counts[i] == world).all())
+    with pytest.raises(Exception, match="stream kernel needs"):
+        _cluster(world, n, 4096, align_blocks=True, kernel="stream").run_round(_srcs(world, n, torch.float32, 0))
