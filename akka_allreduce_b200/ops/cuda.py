@@ -29,6 +29,7 @@ class AarLaunch(C.Structure):
         ("role_s", C.c_int32), ("role_c", C.c_int32), ("nvls_unroll", C.c_int32), ("part_kb", C.c_int32), ("part_sc_kb", C.c_int32), ("overlap_flush", C.c_int32), ("oneshot_pull", C.c_int32),
         ("kernel", C.c_int32), ("self_publish", C.c_int32), ("push_chunks", C.c_int32), ("mc_bcast", C.c_int32),
         ("n", C.c_int64), ("max_chunk", C.c_int64), ("os_cap", C.c_int64), ("block_step", C.c_int64),
+        ("n_cap", C.c_int64), ("block_step_cap", C.c_int64),
         ("L", C.c_int32), ("slot", C.c_int32),
         ("tag", C.c_uint32),
         ("req_reduce", C.c_int32), ("req_complete", C.c_int32), ("gate_count", C.c_int32),

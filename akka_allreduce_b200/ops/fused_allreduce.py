@@ -44,6 +44,7 @@ class RoundLauncher:
         self.algo = algo
         self.timeout_ns = int(timeout_ms * 1e6)
         self.scale, self.normalize = scale, normalize
+        self.th_reduce, self.th_complete = th_reduce, th_complete
         self.req_reduce = geo.req_reduce(th_reduce)
         self.req_complete = geo.req_complete(th_complete)
         self.gate = 0 if th_allreduce is None else gate_count(th_allreduce, geo.world)
@@ -109,6 +110,7 @@ class RoundLauncher:
         a.part_kb = int(os.environ.get("AAR_PART_KB", 64 if (big and not self.stream_expected) else 0))
         a.part_sc_kb = int(os.environ.get("AAR_PART_SC_KB", 0))
         a.n, a.max_chunk, a.os_cap, a.block_step = g.n, g.max_chunk, self.os_cap, g.block_step_arg
+        a.n_cap = a.block_step_cap = 0
         a.L = g.slots
         a.req_reduce, a.req_complete, a.gate_count = self.req_reduce, self.req_complete, self.gate
         a.normalize, a.scale = int(self.normalize), self.scale
@@ -212,6 +214,33 @@ class EmulatedCluster:
             a.op = K.OP_ALLREDUCE
         if round_ is None:
             self.round += 1
+        return outs, counts
+
+    def run_part(self, srcs, inj: Injection | None = None):
+        """One round over a SHORTER message (every ``srcs[i]`` holds m <= n elements) on this cluster's regions: the
+        capacity layout of ``AarLaunch.n_cap`` (strides from n, partition from m).  Needs align_blocks=True.
+        Returns (outs, counts) of m elements each."""
+        g, L = self.geo, self.launcher
+        m = srcs[0].numel()
+        assert not g.reference_partition and 0 < m <= g.n
+        if m == g.n:
+            return self.run_round(srcs, inj)
+        sub = Geometry.make(m, g.max_chunk, g.world, g.slots - 1, True)
+        outs = [torch.empty(m, dtype=L.dtype, device=self.device) for _ in range(self.world)]
+        counts = [torch.empty(m, dtype=torch.int32, device=self.device) for _ in range(self.world)]
+        a = self._a
+        L.fill(a, self.round, inj)
+        a.n, a.block_step, a.n_cap, a.block_step_cap = m, sub.step, g.n, g.step
+        a.req_complete = sub.req_complete(L.th_complete)
+        for i in range(self.world):
+            assert srcs[i].numel() == m and srcs[i].dtype == L.dtype and srcs[i].is_contiguous()
+            a.src[i], a.out[i], a.counts[i] = srcs[i].data_ptr(), outs[i].data_ptr(), counts[i].data_ptr()
+        try:
+            L.launch(a)
+        finally:
+            a.n, a.block_step, a.n_cap, a.block_step_cap = g.n, g.block_step_arg, 0, 0
+            a.req_complete = L.req_complete
+        self.round += 1
         return outs, counts
 
     def set_dead_peers(self, masks: dict) -> None:

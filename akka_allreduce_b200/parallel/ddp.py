@@ -23,7 +23,8 @@ from .engine import DeviceAllreduce, default_uds_dir
 class AllreduceCommHook:
     def __init__(self, rank: int, world: int, device: int, max_chunk_bytes: int = 1 << 20, max_lag: int = 1,
                  th_reduce: float = 1.0, th_complete: float = 1.0, uds_dir: Optional[str] = None,
-                 timeout_ms: float = 30_000.0, algo: str = "auto", ctas: Optional[int] = None):
+                 timeout_ms: float = 30_000.0, algo: str = "auto", ctas: Optional[int] = None,
+                 capacity_bytes: Optional[int] = None):
         self.rank, self.world, self.device_index = rank, world, device
         self.__name__ = self.__qualname__ = "akka_allreduce_b200_fused_allreduce_hook"  # DDP logs the hook's name
         self.device = torch.device("cuda", device)
@@ -32,10 +33,43 @@ class AllreduceCommHook:
         self.uds_dir = uds_dir or default_uds_dir("ddp")
         self.timeout_ms, self.algo, self.ctas = timeout_ms, algo, ctas
         self.stream = torch.cuda.Stream(device=self.device)
+        # One symmetric heap for ALL bucket sizes up to `capacity_bytes` (per dtype), instead of one heap per distinct
+        # size: buckets run as rounds of different lengths on the region of the largest (DeviceAllreduce.allreduce_part).
+        # Pick it >= DDP's bucket_cap_mb (and >= the largest single parameter).  None = one engine per size.
+        self.capacity_bytes = capacity_bytes
+        self._shared: Dict[torch.dtype, DeviceAllreduce] = {}
         self._engines: Dict[Tuple[int, torch.dtype], DeviceAllreduce] = {}
         self._outs: Dict[Tuple[int, torch.dtype], torch.Tensor] = {}  # only used with thresholds below 1
         self.buckets_reduced = 0
         self.kernel_launches = 0
+
+    def _shared_engine(self, numel: int, dtype: torch.dtype) -> Optional[DeviceAllreduce]:
+        """The capacity engine of this dtype if the bucket fits (created collectively on first use)."""
+        if self.capacity_bytes is None:
+            return None
+        esz = torch.empty((), dtype=dtype).element_size()
+        cap = self.capacity_bytes // esz // 128 * 128
+        if numel > cap or cap <= 0:
+            return None
+        eng = self._shared.get(dtype)
+        if eng is None:
+            # two-shot / NVLS only (picked from the capacity): the one-shot and direct forms keep whole messages in rows
+            # of their own and are not laid out for shorter rounds
+            algo = self.algo if self.algo in ("twoshot", "nvls") else ("nvls" if self.world >= 5 else "twoshot")
+            try:
+                eng = DeviceAllreduce(self.rank, self.world, cap, max(1, self.max_chunk_bytes // esz), self.max_lag,
+                                      dtype=dtype, th_reduce=self.th_reduce, th_complete=self.th_complete,
+                                      device=self.device_index, uds_dir=self.uds_dir, align_blocks=True,
+                                      timeout_ms=self.timeout_ms, normalize=True, algo=algo, ctas=self.ctas)
+            except Exception:
+                if algo != "nvls":
+                    raise
+                eng = DeviceAllreduce(self.rank, self.world, cap, max(1, self.max_chunk_bytes // esz), self.max_lag,
+                                      dtype=dtype, th_reduce=self.th_reduce, th_complete=self.th_complete,
+                                      device=self.device_index, uds_dir=self.uds_dir, align_blocks=True,
+                                      timeout_ms=self.timeout_ms, normalize=True, algo="twoshot", ctas=self.ctas)
+            self._shared[dtype] = eng
+        return eng
 
     def _engine(self, numel: int, dtype: torch.dtype) -> DeviceAllreduce:
         key = (numel, dtype)
@@ -54,7 +88,9 @@ class AllreduceCommHook:
 
     def __call__(self, state, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
         buf = bucket.buffer()
-        eng = self._engine(buf.numel(), buf.dtype)
+        shared = self._shared_engine(buf.numel(), buf.dtype)
+        eng = shared if shared is not None else self._engine(buf.numel(), buf.dtype)
+        run = eng.allreduce_part if shared is not None else eng.allreduce
         fut: torch.futures.Future[torch.Tensor] = torch.futures.Future(devices=[self.device])
         self.stream.wait_stream(torch.cuda.current_stream(self.device))  # the bucket's gradients are final
         with torch.cuda.stream(self.stream):
@@ -64,10 +100,10 @@ class AllreduceCommHook:
                 out = self._outs.get((buf.numel(), buf.dtype))
                 if out is None:
                     out = self._outs[(buf.numel(), buf.dtype)] = torch.empty_like(buf)
-                eng.allreduce(buf, out, None, stream=self.stream)
+                run(buf, out, None, stream=self.stream)
                 buf.copy_(out, non_blocking=True)
             else:
-                eng.allreduce(buf, buf, None, stream=self.stream)  # in place: mean over the contributors
+                run(buf, buf, None, stream=self.stream)  # in place: mean over the contributors
             self.kernel_launches += eng.launcher.launches - before
             buf.record_stream(self.stream)
             fut.set_result(buf)  # captures the side stream's position
@@ -75,9 +111,10 @@ class AllreduceCommHook:
         return fut
 
     def close(self) -> None:
-        for eng in self._engines.values():
+        for eng in list(self._engines.values()) + list(self._shared.values()):
             eng.close()
         self._engines.clear()
+        self._shared.clear()
         self._outs.clear()
 
 

@@ -225,6 +225,40 @@ class DeviceAllreduce:
         if round_ is None:
             self.round += 1
 
+    def allreduce_part(self, src: torch.Tensor, out: torch.Tensor, counts: torch.Tensor | None = None,
+                       stream: torch.cuda.Stream | None = None) -> None:
+        """One round over a SHORTER message on this engine's region: ``src.numel() <= n``.  The region, the flags and
+        the ring keep the layout of the capacity ``n`` (row pitch, flags per block); only the partition follows the
+        actual length (``AarLaunch.n_cap``).  Rounds of different lengths are ordinary consecutive rounds of the same
+        ring — same tags, same slots, same back-pressure — which is how one heap serves DDP buckets of several sizes
+        (``AllreduceCommHook(capacity_bytes=...)``).  Every rank must pass the same length for the same round.
+        Needs ``align_blocks=True`` and a two-shot or NVLS engine."""
+        g, l = self.geo, self.launcher
+        m = src.numel()
+        if m == g.n:
+            return self.allreduce(src, out, counts, stream=stream)
+        if g.reference_partition or self.algo not in ("twoshot", "nvls"):
+            raise K.AarError("allreduce_part needs an engine with align_blocks=True and algo twoshot or nvls")
+        if not 0 < m < g.n or out.numel() != m or (counts is not None and counts.numel() != m):
+            raise ValueError(f"allreduce_part: 0 < src.numel() <= {g.n}, out and counts of the same length")
+        if src.dtype != l.dtype or out.dtype != l.dtype:
+            raise ValueError("dtype differs from the engine's")
+        if self.partial_thresholds and self._overlap(src, out):
+            raise ValueError("allreduce in place (out overlaps src) needs thReduce = thComplete = 1")
+        sub = Geometry.make(m, g.max_chunk, g.world, g.slots - 1, True)
+        a = self._launch
+        l.fill(a, self.round, None)
+        a.n, a.block_step, a.n_cap, a.block_step_cap = m, sub.step, g.n, g.step
+        a.req_complete = sub.req_complete(l.th_complete)
+        a.src[0], a.out[0] = src.data_ptr(), out.data_ptr()
+        a.counts[0] = counts.data_ptr() if counts is not None else None
+        try:
+            l.launch(a, stream)
+        finally:
+            a.n, a.block_step, a.n_cap, a.block_step_cap = g.n, g.block_step_arg, 0, 0
+            a.req_complete = l.req_complete
+        self.round += 1
+
     @staticmethod
     def _overlap(x: torch.Tensor, y: torch.Tensor) -> bool:
         return (x.data_ptr() < y.data_ptr() + y.numel() * y.element_size()

@@ -955,9 +955,24 @@ int prepare_round(const AarLaunch* a, KParams& kp, bool& use_stream) {
   if (!a->emu && (a->rank < 0 || a->rank >= a->world)) return fail(AAR_EINVAL, "rank must be in 0..world-1");
   if (a->os_cap < 0) return fail(AAR_EINVAL, "negative one-shot capacity");
   if (a->block_step != 0 && a->block_step * a->world < a->n) return fail(AAR_EINVAL, "block_step too small");
+  // Capacity layout: the region and the scratch may have been laid out for a LARGER message than this round moves.
+  // Offsets and strides (row pitch, flags per block) then come from the capacity, the partition from this round's n;
+  // the kernels only ever use the strides, so rounds of different lengths share one region and one ring.
+  const bool capped = a->n_cap > 0;
+  if (capped) {
+    if (a->n > a->n_cap) return fail(AAR_ETOOBIG, "message longer than the capacity the region was laid out for");
+    if (a->block_step <= 0 || a->block_step_cap <= 0)
+      return fail(AAR_EINVAL, "a capacity layout needs explicit block steps (block_step and block_step_cap)");
+    if (a->block_step > a->block_step_cap || a->block_step_cap * a->world < a->n_cap)
+      return fail(AAR_EINVAL, "block_step must not exceed block_step_cap, and block_step_cap x world must cover n_cap");
+  } else if (a->n_cap < 0 || a->block_step_cap != 0) {
+    return fail(AAR_EINVAL, "block_step_cap without n_cap");
+  }
   kp.a = *a;
   const int wb = wire_bytes_of(a->wire_dtype);
-  kp.sym = SymLayout::make(a->n, a->max_chunk, a->world, a->L, wb, a->os_cap, a->block_step);
+  kp.sym = SymLayout::make(capped ? a->n_cap : a->n, a->max_chunk, a->world, a->L, wb, a->os_cap,
+                           capped ? a->block_step_cap : a->block_step);
+  if (capped) kp.sym.block = a->block_step;  // host arithmetic below is about THIS round (device code reads block_pad / cpb)
   kp.scr = ScratchLayout::make(a->world, kp.sym.cpb);
   kp.part = Partition(a->n, a->world, kp.sym.block);
   kp.total_chunks = total_reduced_chunks(kp.part, a->max_chunk);
@@ -1278,7 +1293,8 @@ int aar_allreduce_round_static_scratch(const AarLaunch* a, void* stream_v) {
   if (a == nullptr) return fail(AAR_EINVAL, "null launch");
   if (a->world < 1 || a->world > AAR_MAX_RANKS || a->n <= 0 || a->max_chunk <= 0)
     return fail(AAR_EINVAL, "bad world/size arguments");
-  const int64_t need = aar_scratch_bytes(a->n, a->max_chunk, a->world, a->block_step);
+  const int64_t need = a->n_cap > 0 ? aar_scratch_bytes(a->n_cap, a->max_chunk, a->world, a->block_step_cap)
+                                    : aar_scratch_bytes(a->n, a->max_chunk, a->world, a->block_step);
   if (need > AAR_STATIC_SCRATCH_PER_RANK)
     return fail(AAR_ETOOBIG, "this configuration needs " + std::to_string(need) +
                                  " bytes of scratch per rank, the built-in scratch holds " +

@@ -65,6 +65,10 @@ typedef struct AarLaunch {
   int64_t n, max_chunk;     /* dataSize, maxChunkSize (elements) */
   int64_t os_cap;           /* one-shot capacity the region was laid out with */
   int64_t block_step;       /* 0 = reference partition ceil(n/world); else an aligned step >= that */
+  int64_t n_cap;            /* 0, or the LARGER message length the region and the scratch were laid out for: this
+                               round then moves n <= n_cap elements through the same region (strides and offsets
+                               from the capacity, partition from n) — how one heap serves buckets of several sizes */
+  int64_t block_step_cap;   /* with n_cap: the block step of the capacity layout (block_step must be set too) */
   int32_t L, slot;          /* ring slots (maxLag+1), round % L */
   uint32_t tag;             /* round + 1 */
   int32_t req_reduce;       /* int(thReduce * P) */

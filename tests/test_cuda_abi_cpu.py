@@ -116,3 +116,18 @@ def test_scratch_words_the_host_writes():
         force, dead, total = (lib.aar_scratch_force_offset(n, mc, P, 0), lib.aar_scratch_dead_offset(n, mc, P, 0),
                               lib.aar_scratch_bytes(n, mc, P, 0))
         assert dead == force + 8 and dead + 4 <= total and force % 4 == 0
+
+
+@pytest.mark.parametrize("kw,needle", [
+    (dict(n=1 << 16, n_cap=1 << 15, block_step=1 << 14, block_step_cap=1 << 13), "capacity"),           # longer than the capacity
+    (dict(n_cap=1 << 18), "explicit block steps"),                                                   # no steps given
+    (dict(n_cap=1 << 18, block_step=1 << 17, block_step_cap=1 << 16), "block_step"),                  # step beyond the capacity's
+    (dict(n_cap=1 << 18, block_step=1 << 14, block_step_cap=1 << 15), "cover n_cap"),                 # capacity step too small
+    (dict(block_step_cap=1 << 14), "without n_cap"),
+])
+def test_capacity_layout_arguments_are_checked(kw, needle):
+    """AarLaunch.n_cap (one region for several message lengths): inconsistent descriptions are refused up front."""
+    lib = K.lib()
+    a = _launch(**kw)
+    assert lib.aar_round_kernel(C.byref(a)) in (-1, -4)
+    assert needle in lib.aar_last_error().decode()

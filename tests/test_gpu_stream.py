@@ -265,3 +265,21 @@ def test_message_length_not_a_multiple_of_the_unit_goes_to_the_generic_kernel():
             assert torch.equal(outs[i], want) and bool((counts[i] == world).all())
     with pytest.raises(Exception, match="stream kernel needs"):
         _cluster(world, n, 4096, align_blocks=True, kernel="stream").run_round(_srcs(world, n, torch.float32, 0))
+
+
+@pytest.mark.xfail(reason="capacity layout (AarLaunch.n_cap): written after the round's GPU budget was spent, not yet run "
+                          "on a GPU; CPU tests cover its argument checks only", strict=False)
+@pytest.mark.parametrize("kernel", ["stream", "generic"])
+def test_rounds_of_different_lengths_share_one_region(kernel):
+    """One region laid out for the largest message serves shorter rounds too (how the DDP hook shares one heap across
+    bucket sizes): strides and flags from the capacity, partition from the actual length, one ring for all of them."""
+    world, cap, mc = 4, 1 << 18, 1 << 13
+    cl = _cluster(world, cap, mc, max_lag=1, timeout_ms=5000, kernel=kernel, align_blocks=True)
+    for r, m in enumerate([cap, 1 << 16, 5 * 4096 + 512, cap, 1024, 3 * (1 << 14) + 128, 512, cap]):
+        srcs = _srcs(world, m, torch.float32, r)
+        outs, counts = cl.run_part(srcs) if m != cap else cl.run_round(srcs)
+        want = _ref_sum(srcs)
+        for i in range(world):
+            assert torch.equal(outs[i][:m], want), f"round {r} length {m} rank {i}"
+            assert bool((counts[i][:m] == world).all())
+    assert cl.timeouts_seen() == [0] * world
