@@ -18,7 +18,7 @@ import torch
 
 from ..ops import cuda as K
 from ..ops.fused_allreduce import Injection, RoundLauncher
-from ..ops.geometry import Geometry, default_ctas
+from ..ops.geometry import Geometry
 
 
 def oneshot_eligible(geo: Geometry, th_reduce: float, th_complete: float, max_lag: int, th_allreduce) -> bool:
