@@ -56,6 +56,11 @@ class ModelConfig:
     notices: bool = False      # skip notices (csrc/cuda/round_common.cuh decide_dest_mask_warp / peers_gone, csrc/host/shm_cluster.cc): a sender
                                # that leaves a peer out records the tag in a per-(dest, src) word outside the slot ring,
                                # and a waiter treats "not arrived + notice >= my tag" as "will never arrive"
+    dead_rank: int = -1        # >= 0: this rank stops for good after finishing round-tag `dies_after` (its process is gone);
+    dies_after: int = 1        # at some later, arbitrary moment the coordinator's removal reaches the survivors as the
+                               # dead-peer mask (one global step): from then on they neither push to it nor wait for it
+                               # (round_common.cuh peers_gone / decide_dest_mask_warp; AllreduceMaster.scala:46-52)
+    announce: bool = True      # False = seeded bug: the removal never reaches the survivors (no dead-peer mask)
     oneshot_backpressure: bool = False  # True = the shipped one-shot kernel (destination mask in its prologue); False = the round-1 kernel without it;
                                         # True models the planned fix (same `done + L >= tag` rule as two-shot)
 
@@ -120,7 +125,7 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
     exact = req_r == P and req_c == P and not cfg.timeouts and not cfg.notices
 
     # rank state: (tag, pc, i, ok_mask, mask)
-    init = (tuple((1, GATE, 0, 0, 0) for _ in range(P)), tuple([0] * lay.size), cfg.giveups if cfg.timeouts else 0)
+    init = (tuple((1, GATE, 0, 0, 0) for _ in range(P)), tuple([0] * lay.size), cfg.giveups if cfg.timeouts else 0, 0)
     parent = {init: None}
     queue = deque([init])
 
@@ -133,8 +138,11 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
 
     def successors(state):
         """Yields (label, next_state) or (label, None, violation)."""
-        ranks, mem, left = state
+        ranks, mem, left, ann = state
         may_give_up = cfg.timeouts and left != 0
+        dead = cfg.dead_rank if ann else -1     # what the survivors KNOW (the mask), not what is true
+        if cfg.dead_rank >= 0 and cfg.announce and not ann and ranks[cfg.dead_rank][1] == END:
+            yield ("coordinator: removal announced (dead-peer mask set)", (ranks, mem, left, 1))
         for q in range(P):
             t, pc, i, ok, m = ranks[q]
             if pc == END:
@@ -146,7 +154,7 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                 nr = ranks[:q] + (new_rank,) + ranks[q + 1:]
                 if gave_up:
                     label += " (gave up)"
-                return (label, (nr, _put(mem, writes) if writes else mem, left - 1 if gave_up and left > 0 else left))
+                return (label, (nr, _put(mem, writes) if writes else mem, left - 1 if gave_up and left > 0 else left, ann))
 
             if pc == GATE and cfg.output_view and i == 0 and t > L and not cfg.oneshot:
                 bad = [o for o in range(P) if mem[lay.sink(q, l, o)] > t - L]
@@ -159,7 +167,8 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                 yield go((t, GATE, 1, 0, 0), [(lay.scat(d, l, q), t) for d in range(P)], label=label + " (caller fills staging)")
             elif pc == GATE:
                 have = sum(1 for s in range(P) if s == q or mem[lay.done(q, s)] + 1 >= t)
-                opened = cfg.gate_count <= 0 or t <= 1 or have >= cfg.gate_count
+                need = min(cfg.gate_count, P - 1) if dead >= 0 else cfg.gate_count   # no more than the live ranks can give
+                opened = cfg.gate_count <= 0 or t <= 1 or have >= need
                 if opened or may_give_up:
                     yield go((t, MASK, 0, 0, 0), gave_up=not opened)
             elif pc == MASK:
@@ -168,9 +177,9 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                 else:
                     okm = 0
                     for d in range(P):
-                        if d == q or mem[lay.done(q, d)] + L >= t:
+                        if d == q or (mem[lay.done(q, d)] + L >= t and d != dead):
                             okm |= 1 << d
-                notes = [(lay.note(d, q), t) for d in range(P) if not (okm >> d) & 1] if cfg.notices else []
+                notes = [(lay.note(d, q), t) for d in range(P) if not (okm >> d) & 1 and d != dead] if cfg.notices else []
                 yield go((t, SDATA, 0, okm, 0), notes)
             elif pc == SDATA:
                 # two-shot: my slice for owner d into d's scat row [me]; one-shot: my whole message, same rows
@@ -187,8 +196,8 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                     if mem[lay.arr(q, l, s)] == t:
                         have |= 1 << s
                 met = bin(have).count("1") >= req_r
-                if not met and cfg.notices:   # everyone who has not arrived has said it never will
-                    gone = [s for s in range(P) if not (have >> s) & 1 and mem[lay.note(q, s)] >= t]
+                if not met and (cfg.notices or dead >= 0):   # everyone who has not arrived is dead or has said it never will
+                    gone = [s for s in range(P) if not (have >> s) & 1 and (s == dead or (cfg.notices and mem[lay.note(q, s)] >= t))]
                     met = bool(gone) and bin(have).count("1") + len(gone) == P
                 if met or may_give_up:
                     yield go((t, RREAD, 0, ok, have), gave_up=not met)
@@ -198,7 +207,7 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                         yield (label, None, f"rank {q} round-tag {t}: contribution of rank {s} in slot {l} carries "
                                             f"tag {mem[lay.scat(q, l, s)]}")
                         return
-                if exact and m != full:
+                if exact and m != full and cfg.dead_rank < 0:
                     yield (label, None, f"rank {q} round-tag {t}: reduced {m:b} instead of all ranks")
                     return
                 if cfg.oneshot:   # one-shot: the local sum IS the result; nothing to broadcast or wait for
@@ -220,8 +229,8 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                     if mem[lay.rfl(q, l, o)] == t:
                         have |= 1 << o
                 met = bin(have).count("1") >= req_c
-                if not met and cfg.notices:
-                    gone = [o for o in range(P) if not (have >> o) & 1 and mem[lay.note(q, o)] >= t]
+                if not met and (cfg.notices or dead >= 0):
+                    gone = [o for o in range(P) if not (have >> o) & 1 and (o == dead or (cfg.notices and mem[lay.note(q, o)] >= t))]
                     met = bool(gone) and bin(have).count("1") + len(gone) == P
                 if met or may_give_up:
                     yield go((t, CREAD, 0, ok, have), gave_up=not met)
@@ -231,15 +240,17 @@ def check(cfg: ModelConfig, max_states: int = 3_000_000, walks: int = 0, seed: i
                         yield (label, None, f"rank {q} round-tag {t}: reduced block of owner {o} in slot {l} "
                                             f"carries tag {mem[lay.sink(q, l, o)]}")
                         return
-                if exact and m != full:
+                if exact and m != full and cfg.dead_rank < 0:
                     yield (label, None, f"rank {q} round-tag {t}: completed with {m:b} instead of all owners")
                     return
                 yield go((t, DONE, 0, ok, 0))
             elif pc == DONE:
                 d = (q + i) % P
-                writes = [(lay.done(d, q), t)]
+                writes = [(lay.done(d, q), t)] if d != dead else []
                 if i + 1 < P:
                     yield go((t, DONE, i + 1, ok, 0), writes)
+                elif q == cfg.dead_rank and t >= cfg.dies_after:
+                    yield go((t, END, 0, 0, 0), writes, label=label + " (and dies)")
                 elif t < T:
                     yield go((t + 1, GATE, 0, 0, 0), writes)
                 else:
@@ -314,11 +325,14 @@ if __name__ == "__main__":
     ap.add_argument("--early-write", action="store_true")
     ap.add_argument("--output-view", action="store_true")
     ap.add_argument("--notices", action="store_true")
+    ap.add_argument("--dead-rank", type=int, default=-1, help="this rank stops for good after round-tag --dies-after")
+    ap.add_argument("--dies-after", type=int, default=1)
     ap.add_argument("--walks", type=int, default=0, help="random executions instead of the exhaustive search")
     ap.add_argument("--seed", type=int, default=0)
     a = ap.parse_args()
     cfg = ModelConfig(a.P, a.L, a.rounds, a.req_reduce, a.req_complete, a.gate, a.timeouts, a.giveups, a.oneshot,
-                      not a.no_backpressure, a.early_write, a.output_view, a.notices, a.oneshot_backpressure)
+                      not a.no_backpressure, a.early_write, a.output_view, a.notices, a.dead_rank, a.dies_after, True,
+                      a.oneshot_backpressure)
     t0 = time.time()
     r = check(cfg, walks=a.walks, seed=a.seed)
     print(f"{cfg}\n  {'OK' if r.ok else 'VIOLATION'}: {r.states} states in {time.time() - t0:.1f}s")

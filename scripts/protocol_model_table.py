@@ -18,6 +18,9 @@ rows = [
  ("thresholds 2/3, no timeouts (liveness)", ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2), {}),
  ("same with skip notices (shipped kernels)", ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2, notices=True), {}),
  ("one slot, no gate, skip notices", ModelConfig(P=2, L=1, rounds=4, notices=True), {}),
+ ("a rank dies after round 1; dead-peer mask, thresholds 1, no timeouts (shipped kernels)", ModelConfig(P=3, L=2, rounds=4, dead_rank=2, dies_after=1), {}),
+ ("same, one slot with the full gate (needs the skip notices: the relaxed gate no longer implies free slots)", ModelConfig(P=3, L=1, rounds=3, gate_count=3, notices=True, dead_rank=0, dies_after=1), {}),
+ ("seeded bug: the removal is never announced", ModelConfig(P=3, L=2, rounds=4, dead_rank=2, dies_after=1, announce=False), {}),
  ("one-shot, 2 slots", ModelConfig(P=3, L=2, rounds=3, oneshot=True), {}),
  ("one-shot, 1 slot, no gate (refused by the ABI)", ModelConfig(P=2, L=1, rounds=3, oneshot=True), {}),
  ("one-shot under timeouts WITHOUT a destination mask (the round-1 kernel: seeded bug)", ModelConfig(P=2, L=2, rounds=4, oneshot=True, timeouts=True), {}),

@@ -115,3 +115,21 @@ def test_skip_notices_make_partial_thresholds_live_without_timeouts():
     assert check(ModelConfig(P=2, L=2, rounds=5, req_reduce=1, req_complete=1, notices=True, timeouts=True)).ok
     assert check(ModelConfig(P=8, L=2, rounds=8, req_reduce=6, req_complete=6, gate_count=6, notices=True),
                  walks=40, seed=4).ok
+
+
+def test_dead_peer_mask_keeps_the_survivors_safe_and_live():
+    """A rank stops for good; at an arbitrary later moment the coordinator's removal reaches the survivors as the
+    dead-peer mask.  With every threshold at 1 and NO timeouts the survivors still finish every round (the waits close
+    on "nothing more can come") and never read a recycled slot; without the announcement they are stuck — the check
+    has teeth."""
+    from akka_allreduce_b200.utils.protocol_model import ModelConfig, check
+
+    for cfg in (ModelConfig(P=3, L=2, rounds=4, dead_rank=2, dies_after=1),
+                ModelConfig(P=3, L=2, rounds=4, gate_count=3, dead_rank=2, dies_after=2),
+                ModelConfig(P=3, L=1, rounds=3, gate_count=3, notices=True, dead_rank=0, dies_after=1),
+                ModelConfig(P=3, L=2, rounds=3, req_reduce=2, req_complete=2, gate_count=2, notices=True, dead_rank=1, dies_after=1),
+                ModelConfig(P=3, L=2, rounds=3, oneshot=True, oneshot_backpressure=True, dead_rank=0, dies_after=1)):
+        r = check(cfg)
+        assert r.ok, (cfg, r.violation)
+    r = check(ModelConfig(P=3, L=2, rounds=4, dead_rank=2, dies_after=1, announce=False))
+    assert not r.ok and r.violation.startswith("stuck")
