@@ -131,3 +131,27 @@ def test_capacity_layout_arguments_are_checked(kw, needle):
     a = _launch(**kw)
     assert lib.aar_round_kernel(C.byref(a)) in (-1, -4)
     assert needle in lib.aar_last_error().decode()
+
+
+def test_slot_views_are_only_handed_out_with_full_thresholds():
+    """Both views bypass the kernel's back-pressure (the caller touches the slot outside the launch).  Round 1 handed
+    `input_view` out with thComplete < 1: a rank could finish round r - L without a slow owner's chunks and overwrite the
+    staging rows that owner was still pulling.  The rule needs no GPU to check."""
+    import types
+
+    import torch
+
+    from akka_allreduce_b200.parallel.engine import DeviceAllreduce
+
+    eng = object.__new__(DeviceAllreduce)
+    eng.rank, eng.world, eng.algo = 0, 4, "nvls"
+    eng.geo = types.SimpleNamespace(n=4096, world=4, total_chunks=8, step=1024, slots=2)
+    eng.launcher = types.SimpleNamespace(dtype=torch.float32, wire_dtype=torch.float32, scale=1.0, req_reduce=4,
+                                         req_complete=6, off_scat=0, off_sink=0)
+    eng._view = lambda off, numel: ("view", off, numel)
+    assert eng.zero_copy_ok and eng.partial_thresholds
+    assert eng.input_view(0) is None and eng.output_view(0) is None          # thComplete 0.75: neither
+    eng.launcher.req_complete = 8
+    assert eng.input_view(1) == ("view", 1 * 4 * 1024 * 4, 4096) and eng.output_view(0) == ("view", 0, 4096)
+    eng.launcher.req_reduce = 3                                               # thReduce below 1: neither, either
+    assert eng.input_view(0) is None and eng.output_view(0) is None
