@@ -4,7 +4,8 @@
     python -m torch.distributed.run --nproc-per-node 8 --master-addr 127.0.0.1 examples/collective_cuda.py
 
 Shows both ways to feed it: ordinary tensors (the kernel stages and flushes them) and the engine's own
-symmetric slots (nothing to copy), plus partial completion: with thReduce = thComplete = 0.75 a rank that
+symmetric slots (nothing to copy), the reduce-scatter / all-gather halves of the round on their own, plus partial
+completion: with thReduce = thComplete = 0.75 a rank that
 stays silent is simply left out and `count` says so.
 """
 import os
@@ -38,6 +39,15 @@ if slot_out is not None:                                                 # zero-
     eng.allreduce(src, slot_out, count)
     torch.cuda.synchronize()
     assert float(slot_out[-1]) == world * (world + 1) / 2
+
+if eng.algo in ("twoshot", "nvls") and eng.launcher.stream_expected:     # the two halves of the round on their own
+    lo, hi = eng.block_range()
+    block = torch.empty(hi - lo, device="cuda")
+    eng.reduce_scatter(x, block)                                         # my block of the sum ...
+    eng.all_gather(block, out, count)                                    # ... and everybody's blocks back together
+    torch.cuda.synchronize()
+    assert float(block[0]) == world * (world + 1) / 2 and float(out[-1]) == world * (world + 1) / 2
+    assert int(count.min()) == 1                                         # one contributor per element: its owner
 eng.close()
 
 if world >= 4:                                                           # partial completion
