@@ -155,3 +155,49 @@ def test_slot_views_are_only_handed_out_with_full_thresholds():
     assert eng.input_view(1) == ("view", 1 * 4 * 1024 * 4, 4096) and eng.output_view(0) == ("view", 0, 4096)
     eng.launcher.req_reduce = 3                                               # thReduce below 1: neither, either
     assert eng.input_view(0) is None and eng.output_view(0) is None
+
+
+def test_engine_round_variants_fill_the_launch_description():
+    """What each public entry of DeviceAllreduce puts into the launch description (no GPU: the launcher is a stub):
+    whole rounds, the reduce-scatter / all-gather halves (op restored afterwards), and a shorter round on the
+    capacity layout (n / block_step of the round, n_cap / block_step_cap of the region, req_complete of the shorter
+    message; restored afterwards)."""
+    import torch
+
+    from akka_allreduce_b200.parallel.engine import DeviceAllreduce
+
+    eng = object.__new__(DeviceAllreduce)
+    eng.rank, eng.world, eng.algo, eng.round = 0, 4, "twoshot", 0
+    eng.geo = Geometry.make(4096, 512, 4, 1, True)
+    seen = []
+
+    class Stub:
+        dtype = wire_dtype = torch.float32
+        scale, req_reduce, req_complete, th_complete, stream_expected = 1.0, 4, 8, 1.0, True
+
+        def fill(self, a, r, inj):
+            a.req_complete = self.req_complete
+
+        def launch(self, a, s):
+            seen.append((a.n, a.block_step, a.n_cap, a.block_step_cap, a.req_complete, a.op))
+
+    eng.launcher, eng._launch, eng._inplace_src = Stub(), K.AarLaunch(), None
+    eng._launch.n, eng._launch.block_step = 4096, eng.geo.block_step_arg
+    x, y = torch.zeros(4096), torch.zeros(4096)
+    eng.allreduce(x, y)
+    eng.allreduce(x, x)                                        # in place: fine on two-shot with thresholds 1
+    eng.allreduce_part(x[:1000], y[:1000])
+    eng.allreduce_part(x, y)                                   # full length = an ordinary round
+    lo, hi = eng.block_range()
+    eng.reduce_scatter(x, y[: hi - lo])
+    eng.all_gather(x[: hi - lo], y)
+    assert seen == [(4096, 1024, 0, 0, 8, K.OP_ALLREDUCE)] * 2 + [(1000, 256, 4096, 1024, 4, K.OP_ALLREDUCE),
+                                                                   (4096, 1024, 0, 0, 8, K.OP_ALLREDUCE),
+                                                                   (4096, 1024, 0, 0, 8, K.OP_REDUCE_SCATTER),
+                                                                   (4096, 1024, 0, 0, 8, K.OP_ALL_GATHER)]
+    a = eng._launch
+    assert (a.n, a.block_step, a.n_cap, a.block_step_cap, a.op) == (4096, 1024, 0, 0, K.OP_ALLREDUCE) and eng.round == 6
+    with pytest.raises(ValueError):
+        eng.allreduce_part(x[:1000], y[:999])
+    with pytest.raises(ValueError):
+        eng.reduce_scatter(x, y)                                # out must be block-sized
