@@ -50,7 +50,7 @@ class ClusterConfig:
     host: str = "127.0.0.1"
     port: int = 2551           # coordinator port (reference default seed node)
     downAfter: float = 10.0    # seconds (auto-down-unreachable-after = 10s)
-    announceRemovals: bool = False  # re-send InitWorkers (peer map refresh) when a worker is removed; always on for cuda
+    announceRemovals: bool = False  # re-send InitWorkers (peer map refresh) when a worker is removed; always on for cuda and shm
     heartbeat: float = 1.0
     loglevel: str = "INFO"
     metricsPort: int = 0       # > 0: the master serves Prometheus metrics on this port (utils/metrics.py)

@@ -29,9 +29,10 @@ class AllreduceMaster:
         opts.down_after_s = config.cluster.downAfter
         opts.verbose = verbose
         mc = config.master_config()
-        # GPU workers must be told when a peer is gone (they would push into and wait on a dead process's memory);
-        # the CPU backends keep the reference's behaviour (stale peers become dead letters) unless asked
-        mc.announce_removals = config.cluster.announceRemovals or config.device.backend == "cuda"
+        # Workers of the device protocol (GPU, or its shared-memory form) must be told when a peer is gone: they would
+        # push into and wait on a dead process's memory.  The TCP backend keeps the reference's behaviour (stale peers
+        # become dead letters) unless asked.
+        mc.announce_removals = config.cluster.announceRemovals or config.device.backend in ("cuda", "shm")
         self._node = host.MasterNode(mc, opts)
         self.port = None
         self.metrics = None

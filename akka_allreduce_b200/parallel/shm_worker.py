@@ -48,6 +48,7 @@ class ShmWorker:
         self._cv = threading.Condition()
         self._init = None
         self._start_round = -1
+        self._dead_mask = 0
         self._stop = False
         self._thread: threading.Thread | None = None
         self._error: BaseException | None = None
@@ -62,8 +63,16 @@ class ShmWorker:
     def _on_message(self, msg) -> None:
         with self._cv:
             if isinstance(msg, host.InitWorkers):
-                if self._init is None:  # later InitWorkers only refresh the peer map (AllreduceWorker.scala:87-89)
+                if self._init is None:
                     self._init = msg
+                # later InitWorkers only refresh the peer map (AllreduceWorker.scala:87-89): ids that are missing from
+                # it belong to workers the master has removed (AllreduceMaster.scala:46-52) — the protocol's dead-peer
+                # mask, as on the GPU: nothing is pushed to them, nothing waits for them.  A replacement that takes
+                # over a vacated id shows up in the next refresh and clears its bit again.
+                alive = set(msg.workers.keys())
+                self._dead_mask = sum(1 << q for q in range(msg.worker_num) if q not in alive and q != msg.dest_id)
+                if self.cluster is not None and self.id >= 0:
+                    self.cluster.set_dead_peers(self.id, self._dead_mask)
             elif isinstance(msg, host.StartAllreduce):
                 self._start_round = max(self._start_round, msg.round)
                 cl, init = self.cluster, self._init
@@ -127,6 +136,8 @@ class ShmWorker:
         self.cluster = host.ShmCluster.attach(sc, self.shm_name, self.id == 0 and not joining_late,
                                               accept_orphan=joining_late)
         cl = self.cluster
+        with self._cv:
+            cl.set_dead_peers(self.id, self._dead_mask)   # (a replacement clears what its predecessor was told)
         self.log.info("----Actor id = %d (shared memory %s); peers = %d; thReduce = %s, thComplete = %s, maxLag = %d; "
                       "region %.1f KiB per rank", self.id, self.shm_name, sc.world, sc.th_reduce, sc.th_complete,
                       sc.max_lag, cl.region_bytes / 1024)

@@ -100,6 +100,55 @@ def test_shm_backend_thresholds_keep_going_without_a_dead_worker():
     assert sum(d >= 145 for d in done) >= 3
 
 
+
+def test_shm_backend_dead_worker_with_full_thresholds_costs_no_timeouts():
+    """Every data threshold at 1 and a 5 s wait bound: without the dead-peer mask each round after a worker's death
+    would sit out the clock.  The coordinator announces the removal (refreshed InitWorkers), the workers turn the ids
+    missing from the peer map into the mask, and the remaining rounds run at full speed with count 3 and zeros /
+    count 0 on the dead owner's block — the GPU backend's behaviour (tests/multi_gpu_kill_worker.py) on the CPU."""
+    P, n, rounds = 4, 64, 400
+    cfg = _cfg(P, n, 8, rounds, th=(0.5, 1.0, 1.0), max_lag=2, timeout_ms=5000.0)
+    master = AllreduceMaster(cfg)
+    port = master.start()
+    seen = [dict() for _ in range(P)]
+    workers = []
+    for i in range(P):
+        def source(req, i=i):
+            return AllReduceInput(np.full(n, float(1 << i), dtype=np.float32))
+
+        def sink(out, i=i):
+            seen[i][out.iteration] = (time.perf_counter(), np.array(out.data), np.array(out.count))
+
+        w = create_worker(source, sink, cfg, master_port=port, shm_name=f"/aar_test_{os.getpid()}_mask")
+        w.start()
+        workers.append(w)
+    try:
+        t0 = time.time()
+        while master.round < 20 and time.time() - t0 < 20:
+            time.sleep(0.002)
+        victim = next(w for w in workers if w.id == 3)      # not the segment's creator
+        victim.stop()
+        t_kill = time.perf_counter()
+        assert master.wait(30.0), f"master stuck at round {master.round}"   # 380 rounds at 5 s each would never make it
+        assert master.alive == 3
+    finally:
+        for w in workers:
+            w.stop()
+        master.stop()
+    survivors = [w for w in workers if w.id != 3]
+    for w in survivors:
+        o = seen[workers.index(w)]
+        assert max(o) == rounds
+        tail = [o[r] for r in range(rounds - 50, rounds + 1)]
+        for _, d, c in tail:
+            assert (c[:48] == 3).all() and (d[:48] == 7.0).all()      # ranks 0-2 on the blocks they own
+            assert (c[48:] == 0).all() and (d[48:] == 0.0).all()      # nobody reduces the dead owner's block
+        # at most a few rounds around the death may have sat out the 5 s clock
+        slow = [r for r in range(1, rounds + 1) if r in o and r - 1 in o and o[r][0] - o[r - 1][0] > 2.0]
+        assert len(slow) <= 3, slow
+        assert o[rounds][0] - t_kill < 25.0
+
+
 def test_shm_backend_cli_processes():
     """Master + 3 worker PROCESSES through the launchers (`--backend shm`), built-in ramp source and assert sink."""
     env = dict(os.environ, PYTHONPATH=ROOT)
