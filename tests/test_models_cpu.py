@@ -97,3 +97,23 @@ def test_bench_roofline_bookkeeping(tmp_path):
     assert r["roofline_busbw_GBps"] == 1400.0 and abs(r["busbw_GBps"] - 573.7) < 1.0 and abs(r["fraction"] - 0.41) < 0.01
     assert bench.roofline(2, "twoshot", n, 0.135, True, str(peaks))["roofline_busbw_GBps"] == 900.0
     assert bench.roofline(8, "oneshot", 1 << 20, 0.02, True, str(peaks))["roofline_busbw_GBps"] == 225.0
+
+
+def test_bench_reference_arm_prints_one_json_line_and_probes_the_box():
+    """Driver contract: `bench.py --impl reference` exits 0 with one JSON line; when the reference cannot run it says
+    why, after actually looking for a JVM toolchain and dependency caches on this machine."""
+    import json
+    import os
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "8", "--steps", "5",
+                        "--warmup", "3"], capture_output=True, text=True, timeout=120)
+    assert p.returncode == 0, p.stderr
+    lines = [l for l in p.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and "unavailable" in d
+    for probe in ("java=", "sbt=", ".ivy2=", "baseline/_ref installed="):
+        assert probe in d["unavailable"]
